@@ -1,0 +1,261 @@
+// Sparse convolution forward, exact fp32 mode (PCC_MODE_EXACT).
+//
+// Output-stationary implicit GEMM: one CTA owns PCC_TILE_M = 128 output rows x TN output
+// channels and walks the kernel offsets k = 0..K-1 (skipping offsets no row of the tile has, per
+// the kernel map's tap mask) and, inside an offset, the input channels in chunks of TK = 32.
+// Gathered input rows and the weight slice are staged into shared memory with cp.async
+// (zero-fill for missing neighbours), 3 stages deep; each thread keeps an 8 x (TN/16) register
+// tile and issues fp32 FFMA in ascending (k, ci) order, which is the oracle's summation order,
+// so the result is bit-identical to oracle/pcc_oracle.cpp::orc_conv.  No atomics.
+//
+// Roofline: FP32 FMA pipe for cin, cout >= 32 (148 SMs x 128 lanes x 2 flop x clock); the
+// gathers are served by L2 because rows are in lexicographic order.
+#include "pcc_common.cuh"
+
+namespace pcc {
+
+constexpr int CE_TM = PCC_TILE_M;  // 128 output rows
+constexpr int CE_TK = 32;          // input channels per stage
+constexpr int CE_THREADS = 256;    // 16 x 16
+constexpr int CE_STAGES = 3;
+constexpr int CE_APITCH = CE_TK + 4;  // floats; keeps 16 B alignment, rows r and r+1 4 banks apart
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, int src_bytes) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(gmem), "r"(src_bytes));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;\n" ::"n"(N));
+}
+
+struct ConvParams {
+  const float* in;
+  const float* weight;
+  const float* bias;
+  const int32_t* nbr;
+  const uint32_t* tapmask;
+  const float* film;
+  const int32_t* film_rows;
+  const float* residual;
+  const int32_t* res_rows;
+  float* out;
+  int64_t nbr_stride, n_out, out_stride;
+  int cin, cout, K, act, film_c;
+  float slope;
+};
+
+template <int TN>
+struct ExactSmem {
+  float a[CE_STAGES][CE_TM][CE_APITCH];
+  float b[CE_STAGES][CE_TK][TN];
+};
+
+// VEC: cin % 4 == 0 && cout % 4 == 0 (16-byte cp.async sources are aligned)
+template <int TN, bool VEC>
+__global__ void __launch_bounds__(CE_THREADS, 2)
+conv_exact_kernel(const ConvParams p) {
+  constexpr int CN = TN / 16;  // output channels per thread
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  ExactSmem<TN>& sm = *reinterpret_cast<ExactSmem<TN>*>(smem_raw);
+
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int64_t tile_base = (int64_t)blockIdx.x * CE_TM;
+  const int co_base = blockIdx.y * TN;
+  const int nchunks = (p.cin + CE_TK - 1) / CE_TK;
+  const uint32_t kfull = p.K >= 32 ? 0xffffffffu : ((1u << p.K) - 1u);
+  const uint32_t mask = p.tapmask ? (p.tapmask[blockIdx.x] & kfull) : kfull;
+  const int nsteps = __popc(mask) * nchunks;
+
+  float acc[8][CN];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int c = 0; c < CN; ++c) acc[i][c] = 0.0f;
+
+  // producer cursor
+  uint32_t pmask = mask;
+  int pk = pmask ? (__ffs(pmask) - 1) : 0;
+  int pchunk = 0;
+
+  auto issue = [&](int stage) {
+    const int ci0 = pchunk * CE_TK;
+    // ---- A: 128 rows x 8 quads; thread -> quad q = tid & 7, rows (tid >> 3) + 32 j
+    {
+      const int q = tid & 7;
+      const int ci = ci0 + q * 4;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int r = (tid >> 3) + 32 * j;
+        const int64_t o = tile_base + r;
+        int idx = -1;
+        if (o < p.n_out) idx = __ldg(p.nbr + (int64_t)pk * p.nbr_stride + o);
+        float* dst = &sm.a[stage][r][q * 4];
+        if (VEC) {
+          const bool ok = idx >= 0 && ci < p.cin;
+          const float* src = ok ? p.in + (int64_t)idx * p.cin + ci : p.in;
+          cp_async16(dst, src, ok ? 16 : 0);
+        } else {
+          float v[4] = {0.f, 0.f, 0.f, 0.f};
+          if (idx >= 0) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+              if (ci + e < p.cin) v[e] = __ldg(p.in + (int64_t)idx * p.cin + ci + e);
+          }
+          *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+        }
+      }
+    }
+    // ---- B: TK rows x TN/4 quads
+    {
+      constexpr int QPR = TN / 4;                 // quads per weight row
+      constexpr int TOTAL = CE_TK * QPR;          // quads per stage
+      const float* wk = p.weight + (int64_t)pk * p.cin * p.cout;
+#pragma unroll
+      for (int t = tid; t < TOTAL; t += CE_THREADS) {
+        const int kk = t / QPR, q = t % QPR;
+        const int ci = ci0 + kk, co = co_base + q * 4;
+        float* dst = &sm.b[stage][kk][q * 4];
+        if (VEC) {
+          const bool ok = ci < p.cin && co < p.cout;
+          const float* src = ok ? wk + (int64_t)ci * p.cout + co : p.weight;
+          cp_async16(dst, src, ok ? 16 : 0);
+        } else {
+          float v[4] = {0.f, 0.f, 0.f, 0.f};
+          if (ci < p.cin) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+              if (co + e < p.cout) v[e] = __ldg(wk + (int64_t)ci * p.cout + co + e);
+          }
+          *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+        }
+      }
+    }
+    // advance cursor
+    if (++pchunk == nchunks) {
+      pchunk = 0;
+      pmask &= pmask - 1;
+      pk = pmask ? (__ffs(pmask) - 1) : 0;
+    }
+  };
+
+  // prologue
+#pragma unroll
+  for (int s = 0; s < CE_STAGES - 1; ++s) {
+    if (s < nsteps) issue(s);
+    cp_async_commit();
+  }
+
+  for (int s = 0; s < nsteps; ++s) {
+    cp_async_wait<CE_STAGES - 2>();
+    __syncthreads();
+    if (s + CE_STAGES - 1 < nsteps) issue((s + CE_STAGES - 1) % CE_STAGES);
+    cp_async_commit();
+
+    const int st = s % CE_STAGES;
+#pragma unroll
+    for (int k4 = 0; k4 < CE_TK / 4; ++k4) {
+      float4 a4[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        a4[i] = *reinterpret_cast<const float4*>(&sm.a[st][ty + 16 * i][k4 * 4]);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float b[CN];
+        const float* brow = &sm.b[st][k4 * 4 + e][0];
+        if (CN == 8) {
+          const float4 b0 = *reinterpret_cast<const float4*>(brow + tx * 4);
+          const float4 b1 = *reinterpret_cast<const float4*>(brow + 64 + tx * 4);
+          b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w;
+          b[4 % CN] = b1.x; b[5 % CN] = b1.y; b[6 % CN] = b1.z; b[7 % CN] = b1.w;
+        } else if (CN == 4) {
+          const float4 b0 = *reinterpret_cast<const float4*>(brow + tx * 4);
+          b[0] = b0.x; b[1 % CN] = b0.y; b[2 % CN] = b0.z; b[3 % CN] = b0.w;
+        } else if (CN == 2) {
+          const float2 b0 = *reinterpret_cast<const float2*>(brow + tx * 2);
+          b[0] = b0.x; b[1 % CN] = b0.y;
+        } else {
+          b[0] = brow[tx];
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float av = e == 0 ? a4[i].x : (e == 1 ? a4[i].y : (e == 2 ? a4[i].z : a4[i].w));
+#pragma unroll
+          for (int c = 0; c < CN; ++c) acc[i][c] = __fmaf_rn(av, b[c], acc[i][c]);
+        }
+      }
+    }
+  }
+  cp_async_wait<0>();
+
+  // ---- epilogue: bias -> activation -> FiLM -> residual -> store
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int64_t o = tile_base + ty + 16 * i;
+    if (o >= p.n_out) continue;
+    int64_t frow = o, rrow = o;
+    if (p.film_c && p.film_rows) frow = __ldg(p.film_rows + o);
+    if (p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
+#pragma unroll
+    for (int c = 0; c < CN; ++c) {
+      const int col = co_base + ((CN == 8) ? ((c >> 2) * 64 + tx * 4 + (c & 3)) : (tx * CN + c));
+      if (col >= p.cout) continue;
+      float v = acc[i][c];
+      if (p.bias) v = __fadd_rn(v, __ldg(p.bias + col));
+      if (p.act == PCC_ACT_RELU)
+        v = fmaxf(v, 0.0f);
+      else if (p.act == PCC_ACT_LEAKY)
+        v = v > 0.0f ? v : __fmul_rn(v, p.slope);
+      if (p.film_c) {
+        float beta = 0.0f, gamma = 0.0f;
+        if (frow >= 0) {
+          const int fc = p.film_c == 1 ? 0 : col;
+          beta = __ldg(p.film + frow * 2 * p.film_c + fc);
+          gamma = __ldg(p.film + frow * 2 * p.film_c + p.film_c + fc);
+        }
+        v = __fadd_rn(__fmul_rn(v, beta), gamma);
+      }
+      if (p.residual) {
+        const float r = rrow >= 0 ? __ldg(p.residual + rrow * p.cout + col) : 0.0f;
+        v = __fadd_rn(v, r);
+      }
+      p.out[o * p.out_stride + col] = v;
+    }
+  }
+}
+
+template <int TN>
+static int launch_exact(const ConvParams& p, cudaStream_t st) {
+  const bool vec = (p.cin % 4 == 0) && (p.cout % 4 == 0) &&
+                   ((reinterpret_cast<uintptr_t>(p.in) & 15) == 0) &&
+                   ((reinterpret_cast<uintptr_t>(p.weight) & 15) == 0);
+  const size_t smem = sizeof(ExactSmem<TN>);
+  dim3 grid((unsigned)ceil_div(p.n_out, CE_TM), (unsigned)ceil_div(p.cout, TN));
+  if (vec) {
+    PCC_CHECK_CUDA(cudaFuncSetAttribute(conv_exact_kernel<TN, true>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    conv_exact_kernel<TN, true><<<grid, CE_THREADS, smem, st>>>(p);
+  } else {
+    PCC_CHECK_CUDA(cudaFuncSetAttribute(conv_exact_kernel<TN, false>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    conv_exact_kernel<TN, false><<<grid, CE_THREADS, smem, st>>>(p);
+  }
+  PCC_CHECK_LAUNCH("conv_exact_kernel");
+  return PCC_OK;
+}
+
+int conv_exact(const pcc_conv_args* a, cudaStream_t st) {
+  ConvParams p;
+  p.in = a->in; p.weight = a->weight; p.bias = a->bias; p.nbr = a->nbr; p.tapmask = a->tapmask;
+  p.film = a->film; p.film_rows = a->film_rows; p.residual = a->residual; p.res_rows = a->res_rows;
+  p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
+  p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope;
+  if (a->cout > 64) return launch_exact<128>(p, st);
+  if (a->cout > 32) return launch_exact<64>(p, st);
+  if (a->cout > 16) return launch_exact<32>(p, st);
+  return launch_exact<16>(p, st);
+}
+
+}  // namespace pcc

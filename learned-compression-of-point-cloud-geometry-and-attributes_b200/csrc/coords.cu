@@ -1,0 +1,484 @@
+// Coordinate handling: key packing, canonical sort, hash build/probe, stride-2 and generative
+// output maps, kernel maps.  Replaces MinkowskiEngine's coordinate manager on the reference
+// path (see include/pcc_b200.h for the call sites).  All HBM-bound integer work.
+#include <cub/device/device_radix_sort.cuh>
+
+#include "pcc_common.cuh"
+
+namespace pcc {
+
+constexpr int THREADS = 256;
+
+static inline unsigned grid_for(int64_t n, int threads = THREADS) {
+  { const int64_t g = ceil_div(n, threads); return (unsigned)(g < 1 ? 1 : g); }
+}
+
+// ---------------------------------------------------------------- pack / unpack
+__global__ void pack_kernel(const int4* __restrict__ coords, int64_t n, uint64_t* __restrict__ keys,
+                            int32_t* __restrict__ status) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int4 c = coords[i];
+  if (status && !(coord_in_range(c.y) && coord_in_range(c.z) && coord_in_range(c.w) && c.x >= 0 &&
+                  c.x < 65536))
+    atomicOr(status, 1);
+  keys[i] = pack_key(c.x, c.y, c.z, c.w);
+}
+
+__global__ void unpack_kernel(const uint64_t* __restrict__ keys, int64_t n, int4* __restrict__ coords) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int4 c;
+  unpack_key(keys[i], c.x, c.y, c.z, c.w);
+  coords[i] = c;
+}
+
+__global__ void iota_kernel(int32_t* __restrict__ v, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) v[i] = (int32_t)i;
+}
+
+__global__ void take_keys_kernel(const uint64_t* __restrict__ keys, const int32_t* __restrict__ rows,
+                                 int64_t n, uint64_t* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = keys[rows[i]];
+}
+
+// ---------------------------------------------------------------- hash build / probe
+__global__ void hash_fill_kernel(uint64_t* __restrict__ tkeys, int64_t cap) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < cap) tkeys[i] = HASH_EMPTY;
+}
+
+__global__ void hash_insert_kernel(const uint64_t* __restrict__ keys, int64_t n,
+                                   uint64_t* __restrict__ tkeys, int32_t* __restrict__ tvals,
+                                   uint64_t cap_mask) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t key = keys[i];
+  uint64_t b = (hash_mix(key) & cap_mask) & ~(uint64_t)(HASH_BUCKET - 1);
+  for (;;) {
+#pragma unroll
+    for (int s = 0; s < HASH_BUCKET; ++s) {
+      unsigned long long* slot = reinterpret_cast<unsigned long long*>(tkeys + b + s);
+      unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(slot);
+      if (cur == HASH_EMPTY) cur = atomicCAS(slot, (unsigned long long)HASH_EMPTY, (unsigned long long)key);
+      if (cur == HASH_EMPTY || cur == key) {  // claimed (or duplicate key: last writer wins)
+        tvals[b + s] = (int32_t)i;
+        return;
+      }
+    }
+    b = (b + HASH_BUCKET) & cap_mask;
+  }
+}
+
+__global__ void hash_probe_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict__ tvals,
+                                  uint64_t cap_mask, const uint64_t* __restrict__ q, int64_t nq,
+                                  int32_t* __restrict__ rows) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nq) rows[i] = hash_find(tkeys, tvals, cap_mask, q[i]);
+}
+
+// ---------------------------------------------------------------- stride map
+// parent key = floor(c / ts) * ts per spatial axis; ts is a power of two on this path but any
+// positive stride is handled (floor division, valid for negative coordinates).
+__device__ __forceinline__ int floor_to(int v, int ts) {
+  int q = v / ts;
+  if ((v % ts) != 0 && v < 0) --q;
+  return q * ts;
+}
+
+__global__ void stride_keys_kernel(const uint64_t* __restrict__ keys, int64_t n, int ts,
+                                   uint64_t* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int b, x, y, z;
+  unpack_key(keys[i], b, x, y, z);
+  out[i] = pack_key(b, floor_to(x, ts), floor_to(y, ts), floor_to(z, ts));
+}
+
+// flags[i] = 1 when sorted[i] starts a new run
+__global__ void head_flags_kernel(const uint64_t* __restrict__ sorted, int64_t n, int32_t* __restrict__ flags) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) flags[i] = (i == 0 || sorted[i] != sorted[i - 1]) ? 1 : 0;
+}
+
+__global__ void compact_heads_kernel(const uint64_t* __restrict__ sorted, int64_t n,
+                                     const int32_t* __restrict__ pos, uint64_t* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && (i == 0 || sorted[i] != sorted[i - 1])) out[pos[i]] = sorted[i];
+}
+
+// ---------------------------------------------------------------- generative expand
+// Candidate q = p + d * ts_out (ts_out = ts_in / 2).  Along an axis with d != 0, q lies between
+// p and p + 2 d ts_out, so the parents that also generate q are p + (e .* d) * ts_in for
+// e in {0,1}^3 (e_a = 0 where d_a = 0).  p owns q iff none of those that is lexicographically
+// smaller than p exists.  The alternatives are among p's 26 coarse neighbours, so one
+// 27-neighbour probe per parent decides ownership of all 27 candidates.
+__device__ __forceinline__ uint32_t coarse_neighbour_mask(const uint64_t* tkeys, const int32_t* tvals,
+                                                          uint64_t cap_mask, int b, int x, int y, int z,
+                                                          int ts) {
+  uint32_t m = 0;
+#pragma unroll 1
+  for (int k = 0; k < 27; ++k) {
+    const int dx = k % 3 - 1, dy = (k / 3) % 3 - 1, dz = k / 9 - 1;
+    if (k == 13) {
+      m |= 1u << 13;
+      continue;
+    }
+    const int qx = x + dx * ts, qy = y + dy * ts, qz = z + dz * ts;
+    if (coord_in_range(qx) && coord_in_range(qy) && coord_in_range(qz) &&
+        hash_find(tkeys, tvals, cap_mask, pack_key(b, qx, qy, qz)) >= 0)
+      m |= 1u << k;
+  }
+  return m;
+}
+
+// bit k of the result: this parent owns candidate d_k
+__device__ __forceinline__ uint32_t owned_candidates(uint32_t nmask) {
+  uint32_t own = 0;
+  for (int k = 0; k < 27; ++k) {
+    const int d[3] = {k % 3 - 1, (k / 3) % 3 - 1, k / 9 - 1};
+    bool owner = true;
+    for (int e = 1; e < 8 && owner; ++e) {
+      int a[3];
+      bool valid = true;
+      for (int ax = 0; ax < 3; ++ax) {
+        const int on = (e >> ax) & 1;
+        if (on && d[ax] == 0) valid = false;
+        a[ax] = on ? d[ax] : 0;
+      }
+      if (!valid) continue;
+      // lexicographic order is (x, y, z): first non-zero component decides
+      const int first = a[0] != 0 ? a[0] : (a[1] != 0 ? a[1] : a[2]);
+      if (first < 0) {
+        const int kk = (a[0] + 1) + 3 * (a[1] + 1) + 9 * (a[2] + 1);
+        if (nmask & (1u << kk)) owner = false;
+      }
+    }
+    if (owner) own |= 1u << k;
+  }
+  return own;
+}
+
+__global__ void expand_count_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict__ tvals,
+                                    uint64_t cap_mask, const uint64_t* __restrict__ keys, int64_t n,
+                                    int kernel_size, int ts_in, uint32_t* __restrict__ own,
+                                    int32_t* __restrict__ counts) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t o;
+  if (kernel_size == 3) {
+    int b, x, y, z;
+    unpack_key(keys[i], b, x, y, z);
+    o = owned_candidates(coarse_neighbour_mask(tkeys, tvals, cap_mask, b, x, y, z, ts_in));
+  } else if (kernel_size == 2) {
+    o = 0xFFu;  // the 8 children of distinct parents are disjoint
+  } else {
+    o = 1u;
+  }
+  own[i] = o;
+  counts[i] = __popc(o);
+}
+
+__global__ void expand_emit_kernel(const uint64_t* __restrict__ keys, int64_t n, int kernel_size,
+                                   int ts_out, const uint32_t* __restrict__ own,
+                                   const int32_t* __restrict__ pos, uint64_t* __restrict__ out,
+                                   int32_t* __restrict__ status) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int b, x, y, z;
+  unpack_key(keys[i], b, x, y, z);
+  uint32_t o = own[i];
+  int64_t w = pos[i];
+  const int lo = kernel_size == 3 ? -1 : 0;
+  while (o) {
+    const int k = __ffs(o) - 1;
+    o &= o - 1;
+    const int dx = k % kernel_size + lo, dy = (k / kernel_size) % kernel_size + lo,
+              dz = k / (kernel_size * kernel_size) + lo;
+    const int qx = x + dx * ts_out, qy = y + dy * ts_out, qz = z + dz * ts_out;
+    if (!(coord_in_range(qx) && coord_in_range(qy) && coord_in_range(qz))) atomicOr(status, 1);
+    out[w++] = pack_key(b, qx, qy, qz);
+  }
+}
+
+// ---------------------------------------------------------------- kernel map
+// One thread per output row, looping over the K offsets: key reads and nbr writes are coalesced
+// across the warp (nbr is offset-major), the warp votes the per-tile tap mask, and the K
+// independent probes per thread give the memory system K-deep parallelism.
+template <int KS>
+__global__ void __launch_bounds__(PCC_TILE_M)
+kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict__ tvals,
+                  uint64_t cap_mask, const uint64_t* __restrict__ out_keys, int64_t n_out, int step,
+                  int in_align, int32_t* __restrict__ nbr, int64_t nbr_stride,
+                  uint32_t* __restrict__ tapmask) {
+  constexpr int K = KS * KS * KS;
+  constexpr int LO = (KS == 3) ? -1 : 0;
+  __shared__ uint32_t smask;
+  if (threadIdx.x == 0) smask = 0;
+  __syncthreads();
+  const int64_t o = (int64_t)blockIdx.x * PCC_TILE_M + threadIdx.x;
+  const bool live = o < n_out;
+  int b = 0, x = 0, y = 0, z = 0;
+  if (live) unpack_key(out_keys[o], b, x, y, z);
+  uint32_t mine = 0;
+  const int amask = in_align - 1;  // in_align is a power of two
+#pragma unroll 3
+  for (int k = 0; k < K; ++k) {
+    const int dx = k % KS + LO, dy = (k / KS) % KS + LO, dz = k / (KS * KS) + LO;
+    const int qx = x + dx * step, qy = y + dy * step, qz = z + dz * step;
+    int r = -1;
+    if (live && coord_in_range(qx) && coord_in_range(qy) && coord_in_range(qz) &&
+        (((qx | qy | qz) & amask) == 0))
+      r = hash_find(tkeys, tvals, cap_mask, pack_key(b, qx, qy, qz));
+    if (live) nbr[(int64_t)k * nbr_stride + o] = r;
+    if (r >= 0) mine |= 1u << k;
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) mine |= __shfl_xor_sync(0xffffffffu, mine, s);
+  if ((threadIdx.x & 31) == 0 && mine) atomicOr(&smask, mine);
+  __syncthreads();
+  if (threadIdx.x == 0 && tapmask) tapmask[blockIdx.x] = smask;
+}
+
+// ---------------------------------------------------------------- sort helpers
+static size_t cub_sort_pairs_bytes(int64_t n) {
+  size_t bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
+                                  (const int32_t*)nullptr, (int32_t*)nullptr, (int)n);
+  return bytes;
+}
+static size_t cub_sort_keys_bytes(int64_t n) {
+  size_t bytes = 0;
+  cub::DeviceRadixSort::SortKeys(nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr, (int)n);
+  return bytes;
+}
+
+static int sort_keys_only(const uint64_t* in, uint64_t* out, int64_t n, void* ws, size_t ws_bytes,
+                          cudaStream_t st) {
+  if (n == 0) return PCC_OK;
+  size_t need = ws_bytes;
+  PCC_CHECK_CUDA(cub::DeviceRadixSort::SortKeys(ws, need, in, out, (int)n, 0, 64, st));
+  return PCC_OK;
+}
+
+}  // namespace pcc
+
+using namespace pcc;
+
+extern "C" {
+
+int pcc_coords_pack(const int32_t* coords, int64_t n, uint64_t* keys, int32_t* status, void* stream) {
+  PCC_REQUIRE(n >= 0 && (n == 0 || (coords && keys)), "null pointer");
+  if (n == 0) return PCC_OK;
+  pack_kernel<<<grid_for(n), THREADS, 0, (cudaStream_t)stream>>>((const int4*)coords, n, keys, status);
+  PCC_CHECK_LAUNCH("pack_kernel");
+  return PCC_OK;
+}
+
+int pcc_coords_unpack(const uint64_t* keys, int64_t n, int32_t* coords, void* stream) {
+  PCC_REQUIRE(n >= 0 && (n == 0 || (coords && keys)), "null pointer");
+  if (n == 0) return PCC_OK;
+  unpack_kernel<<<grid_for(n), THREADS, 0, (cudaStream_t)stream>>>(keys, n, (int4*)coords);
+  PCC_CHECK_LAUNCH("unpack_kernel");
+  return PCC_OK;
+}
+
+size_t pcc_sort_ws_bytes(int64_t n) {
+  if (n <= 0) return 256;
+  return align_up(cub_sort_pairs_bytes(n), 256) + align_up((size_t)n * 4, 256);
+}
+
+int pcc_sort_keys(const uint64_t* keys_in, int64_t n, uint64_t* keys_out, int32_t* perm_out, void* ws,
+                  size_t ws_bytes, void* stream) {
+  PCC_REQUIRE(n >= 0 && n < (1ll << 31), "n out of range");
+  if (n == 0) return PCC_OK;
+  PCC_REQUIRE(keys_in && keys_out && ws, "null pointer");
+  PCC_REQUIRE(ws_bytes >= pcc_sort_ws_bytes(n), "workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!perm_out) return sort_keys_only(keys_in, keys_out, n, ws, ws_bytes, st);
+  size_t cub_bytes = align_up(cub_sort_pairs_bytes(n), 256);
+  int32_t* iota = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(ws) + cub_bytes);
+  iota_kernel<<<grid_for(n), THREADS, 0, st>>>(iota, n);
+  PCC_CHECK_LAUNCH("iota_kernel");
+  PCC_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(ws, cub_bytes, keys_in, keys_out, iota, perm_out,
+                                                 (int)n, 0, 64, st));
+  return PCC_OK;
+}
+
+int pcc_take_keys(const uint64_t* keys, const int32_t* rows, int64_t n, uint64_t* out, void* stream) {
+  if (n == 0) return PCC_OK;
+  PCC_REQUIRE(keys && rows && out, "null pointer");
+  take_keys_kernel<<<grid_for(n), THREADS, 0, (cudaStream_t)stream>>>(keys, rows, n, out);
+  PCC_CHECK_LAUNCH("take_keys_kernel");
+  return PCC_OK;
+}
+
+int64_t pcc_hash_capacity(int64_t n) {
+  int64_t cap = 1024;
+  while (cap < 2 * n) cap <<= 1;
+  return cap;
+}
+
+int pcc_hash_build(const uint64_t* keys, int64_t n, uint64_t* tkeys, int32_t* tvals, int64_t cap,
+                   void* stream) {
+  PCC_REQUIRE(tkeys && tvals, "null table");
+  PCC_REQUIRE(cap >= 1024 && (cap & (cap - 1)) == 0 && cap >= 2 * n, "capacity must be a power of two >= 2n");
+  cudaStream_t st = (cudaStream_t)stream;
+  hash_fill_kernel<<<grid_for(cap), THREADS, 0, st>>>(tkeys, cap);
+  PCC_CHECK_LAUNCH("hash_fill_kernel");
+  if (n > 0) {
+    PCC_REQUIRE(keys, "null keys");
+    hash_insert_kernel<<<grid_for(n), THREADS, 0, st>>>(keys, n, tkeys, tvals, (uint64_t)cap - 1);
+    PCC_CHECK_LAUNCH("hash_insert_kernel");
+  }
+  return PCC_OK;
+}
+
+int pcc_hash_probe(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, const uint64_t* q_keys,
+                   int64_t nq, int32_t* rows, void* stream) {
+  if (nq == 0) return PCC_OK;
+  PCC_REQUIRE(tkeys && tvals && q_keys && rows, "null pointer");
+  PCC_REQUIRE((cap & (cap - 1)) == 0, "capacity must be a power of two");
+  hash_probe_kernel<<<grid_for(nq), THREADS, 0, (cudaStream_t)stream>>>(tkeys, tvals, (uint64_t)cap - 1,
+                                                                        q_keys, nq, rows);
+  PCC_CHECK_LAUNCH("hash_probe_kernel");
+  return PCC_OK;
+}
+
+// ws layout for stride / expand:  [A: raw keys][B: flags/pos int32][scan ws][cub ws]
+static size_t unique_ws_bytes(int64_t m) {
+  return align_up((size_t)m * 8, 256) * 2 + align_up((size_t)m * 4, 256) + scan_ws_bytes(m) +
+         align_up(cub_sort_keys_bytes(m), 256) + 256;
+}
+
+// sorts raw[m] and writes the unique keys to out_keys; returns count through the host pointer
+static int sort_unique(uint64_t* raw, int64_t m, uint64_t* out_keys, int64_t* n_out, char* ws,
+                       size_t ws_bytes, cudaStream_t st) {
+  // raw lives at ws offset 0 (caller filled it)
+  size_t off = align_up((size_t)m * 8, 256);
+  uint64_t* sorted = reinterpret_cast<uint64_t*>(ws + off);
+  off += align_up((size_t)m * 8, 256);
+  int32_t* flags = reinterpret_cast<int32_t*>(ws + off);
+  off += align_up((size_t)m * 4, 256);
+  void* scan_ws = ws + off;
+  off += scan_ws_bytes(m);
+  int32_t* total = reinterpret_cast<int32_t*>(ws + off);
+  off += 256;
+  void* cub_ws = ws + off;
+  size_t cub_bytes = ws_bytes - off;
+  int rc = sort_keys_only(raw, sorted, m, cub_ws, cub_bytes, st);
+  if (rc) return rc;
+  head_flags_kernel<<<grid_for(m), THREADS, 0, st>>>(sorted, m, flags);
+  PCC_CHECK_LAUNCH("head_flags_kernel");
+  rc = exclusive_scan_i32(flags, flags, m, total, scan_ws, st);
+  if (rc) return rc;
+  compact_heads_kernel<<<grid_for(m), THREADS, 0, st>>>(sorted, m, flags, out_keys);
+  PCC_CHECK_LAUNCH("compact_heads_kernel");
+  int32_t h = 0;
+  PCC_CHECK_CUDA(cudaMemcpyAsync(&h, total, 4, cudaMemcpyDeviceToHost, st));
+  PCC_CHECK_CUDA(cudaStreamSynchronize(st));
+  *n_out = h;
+  return PCC_OK;
+}
+
+size_t pcc_stride_ws_bytes(int64_t n) { return unique_ws_bytes(n > 0 ? n : 1); }
+
+int pcc_coords_stride(const uint64_t* keys, int64_t n, int32_t ts_out, uint64_t* out_keys, int64_t* n_out,
+                      void* ws, size_t ws_bytes, void* stream) {
+  PCC_REQUIRE(n_out, "null n_out");
+  *n_out = 0;
+  if (n == 0) return PCC_OK;
+  PCC_REQUIRE(keys && out_keys && ws && ts_out > 0, "bad argument");
+  PCC_REQUIRE(ws_bytes >= pcc_stride_ws_bytes(n), "workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  uint64_t* raw = reinterpret_cast<uint64_t*>(ws);
+  stride_keys_kernel<<<grid_for(n), THREADS, 0, st>>>(keys, n, ts_out, raw);
+  PCC_CHECK_LAUNCH("stride_keys_kernel");
+  return sort_unique(raw, n, out_keys, n_out, reinterpret_cast<char*>(ws), ws_bytes, st);
+}
+
+size_t pcc_expand_ws_bytes(int64_t n, int kernel_size) {
+  if (n <= 0) n = 1;
+  const int64_t m = n * kernel_size * kernel_size * kernel_size;
+  // own[n] u32 | counts/pos[n] i32 | scan ws | total | raw[m] u64 | cub
+  return align_up((size_t)n * 4, 256) * 2 + scan_ws_bytes(n) + 512 + align_up((size_t)m * 8, 256) +
+         align_up(cub_sort_keys_bytes(m), 256);
+}
+
+int pcc_coords_expand(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, const uint64_t* keys,
+                      int64_t n, int kernel_size, int32_t ts_in, uint64_t* out_keys, int64_t* n_out,
+                      void* ws, size_t ws_bytes, void* stream) {
+  PCC_REQUIRE(n_out, "null n_out");
+  *n_out = 0;
+  if (n == 0) return PCC_OK;
+  PCC_REQUIRE(kernel_size >= 1 && kernel_size <= 3, "kernel_size must be 1, 2 or 3");
+  PCC_REQUIRE(keys && out_keys && ws && tkeys && tvals, "null pointer");
+  PCC_REQUIRE(ts_in >= 2 && (ts_in % 2) == 0, "input tensor stride must be even");
+  PCC_REQUIRE(ws_bytes >= pcc_expand_ws_bytes(n, kernel_size), "workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  char* w = reinterpret_cast<char*>(ws);
+  size_t off = 0;
+  uint32_t* own = reinterpret_cast<uint32_t*>(w + off);
+  off += align_up((size_t)n * 4, 256);
+  int32_t* pos = reinterpret_cast<int32_t*>(w + off);
+  off += align_up((size_t)n * 4, 256);
+  void* scan_ws = w + off;
+  off += scan_ws_bytes(n);
+  int32_t* total = reinterpret_cast<int32_t*>(w + off);
+  int32_t* status = total + 1;
+  off += 512;
+  uint64_t* raw = reinterpret_cast<uint64_t*>(w + off);
+  PCC_CHECK_CUDA(cudaMemsetAsync(total, 0, 8, st));
+  expand_count_kernel<<<grid_for(n), THREADS, 0, st>>>(tkeys, tvals, (uint64_t)cap - 1, keys, n,
+                                                       kernel_size, ts_in, own, pos);
+  PCC_CHECK_LAUNCH("expand_count_kernel");
+  int rc = exclusive_scan_i32(pos, pos, n, total, scan_ws, st);
+  if (rc) return rc;
+  expand_emit_kernel<<<grid_for(n), THREADS, 0, st>>>(keys, n, kernel_size, ts_in / 2, own, pos, raw, status);
+  PCC_CHECK_LAUNCH("expand_emit_kernel");
+  int32_t h[2] = {0, 0};
+  PCC_CHECK_CUDA(cudaMemcpyAsync(h, total, 8, cudaMemcpyDeviceToHost, st));
+  PCC_CHECK_CUDA(cudaStreamSynchronize(st));
+  if (h[1]) {
+    set_error("pcc_coords_expand: generated coordinate outside the packable range");
+    return PCC_ERR_CAPACITY;
+  }
+  const int64_t m = h[0];
+  off += align_up((size_t)(n * kernel_size * kernel_size * kernel_size) * 8, 256);
+  rc = sort_keys_only(raw, out_keys, m, w + off, ws_bytes - off, st);
+  if (rc) return rc;
+  *n_out = m;
+  return PCC_OK;
+}
+
+int pcc_kernel_map(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, const uint64_t* out_keys,
+                   int64_t n_out, int kernel_size, int32_t step, int32_t in_align, int32_t* nbr,
+                   int64_t nbr_stride, uint32_t* tapmask, void* stream) {
+  if (n_out == 0) return PCC_OK;
+  PCC_REQUIRE(tkeys && tvals && out_keys && nbr, "null pointer");
+  PCC_REQUIRE(nbr_stride >= n_out, "nbr_stride < n_out");
+  PCC_REQUIRE(in_align > 0 && (in_align & (in_align - 1)) == 0, "in_align must be a power of two");
+  PCC_REQUIRE((cap & (cap - 1)) == 0, "capacity must be a power of two");
+  cudaStream_t st = (cudaStream_t)stream;
+  const unsigned grid = (unsigned)ceil_div(n_out, PCC_TILE_M);
+  const uint64_t cm = (uint64_t)cap - 1;
+  switch (kernel_size) {
+    case 1:
+      kernel_map_kernel<1><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask);
+      break;
+    case 2:
+      kernel_map_kernel<2><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask);
+      break;
+    case 3:
+      kernel_map_kernel<3><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask);
+      break;
+    default:
+      PCC_REQUIRE(false, "kernel_size must be 1, 2 or 3");
+  }
+  PCC_CHECK_LAUNCH("kernel_map_kernel");
+  return PCC_OK;
+}
+
+}  // extern "C"
