@@ -1,0 +1,336 @@
+"""CompressAI-shaped entropy modules over the B200 kernels and the C++ range coder.
+
+Exports the names the reference imports (model/entropy_models.py:9-10, model/model.py:4):
+``EntropyBottleneck``, ``GaussianConditional``, ``CompressionModel`` — same constructor
+arguments, parameter / buffer names (``quantiles``, ``_matrix{i}``, ``_bias{i}``, ``_factor{i}``,
+``_quantized_cdf``, ``_cdf_length``, ``_offset``, ``scale_table`` …) and call signatures
+(tensors shaped [1, C, N]).  Semantics: SURVEY.md Appendix B.
+
+Device work (quantise, CDF index, likelihood) runs in pcc_* kernels; the range coder is the
+reference's sequential CPU algorithm (csrc/host_coder.cpp) and its time is accumulated in
+``coder_stats`` so callers can report it separately from the GPU path.
+"""
+import math
+import time
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import ops
+from ._lib import PccError
+
+coder_stats = {"encode_s": 0.0, "decode_s": 0.0, "d2h_s": 0.0, "h2d_s": 0.0, "symbols": 0,
+               "d2h_bytes": 0, "h2d_bytes": 0}
+
+
+def reset_coder_stats():
+    for k in coder_stats:
+        coder_stats[k] = 0 if isinstance(coder_stats[k], int) else 0.0
+
+
+def get_scale_table(min=0.11, max=256, levels=64):
+    """compressai.models.utils.get_scale_table."""
+    return torch.exp(torch.linspace(math.log(min), math.log(max), levels))
+
+
+class LowerBound(nn.Module):
+    """compressai.ops.LowerBound (forward only): max(x, bound); carries the ``bound`` buffer."""
+
+    def __init__(self, bound):
+        super().__init__()
+        self.register_buffer("bound", torch.Tensor([float(bound)]))
+
+    def forward(self, x):
+        return torch.max(x, self.bound.to(x.device))
+
+
+def _rows_cn(x):
+    """[1, C, N] (typically ``F.t().unsqueeze(0)``) -> contiguous row-major [N, C] without a copy
+    when the input is a transposed view."""
+    if x.dim() != 3 or x.shape[0] != 1:
+        raise PccError("entropy modules take [1, C, N] tensors (batch of one, as the reference)")
+    t = x[0].t()
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _to_host(t):
+    t0 = time.perf_counter()
+    a = t.cpu().numpy()
+    coder_stats["d2h_s"] += time.perf_counter() - t0
+    coder_stats["d2h_bytes"] += a.nbytes
+    return a
+
+
+def _to_dev(a, device):
+    t0 = time.perf_counter()
+    t = torch.from_numpy(a).to(device)
+    coder_stats["h2d_s"] += time.perf_counter() - t0
+    coder_stats["h2d_bytes"] += a.nbytes
+    return t
+
+
+class EntropyModel(nn.Module):
+    def __init__(self, likelihood_bound=1e-9, entropy_coder=None, entropy_coder_precision=16):
+        super().__init__()
+        self.entropy_coder_precision = int(entropy_coder_precision)
+        self.use_likelihood_bound = likelihood_bound > 0
+        self._likelihood_bound = float(likelihood_bound)
+        if self.use_likelihood_bound:
+            self.likelihood_lower_bound = LowerBound(likelihood_bound)
+        self.register_buffer("_offset", torch.IntTensor())
+        self.register_buffer("_quantized_cdf", torch.IntTensor())
+        self.register_buffer("_cdf_length", torch.IntTensor())
+        self._host_tables = None
+        self._dev_cache = {}
+
+    def _set_tables(self, cdf, length, offset):
+        self._host_tables = (np.ascontiguousarray(cdf, np.int32), np.ascontiguousarray(length, np.int32),
+                             np.ascontiguousarray(offset, np.int32))
+        dev = self._quantized_cdf.device
+        self._quantized_cdf = torch.from_numpy(self._host_tables[0].copy()).to(dev)
+        self._cdf_length = torch.from_numpy(self._host_tables[1].copy()).to(dev)
+        self._offset = torch.from_numpy(self._host_tables[2].copy()).to(dev)
+        self._dev_cache = {}
+
+    def _tables(self):
+        if self._host_tables is None:
+            if self._quantized_cdf.numel() == 0:
+                raise PccError("entropy model not initialised: call update() before compress()")
+            self._host_tables = (self._quantized_cdf.cpu().numpy().astype(np.int32),
+                                 self._cdf_length.cpu().numpy().astype(np.int32),
+                                 self._offset.cpu().numpy().astype(np.int32))
+        return self._host_tables
+
+    def _encode(self, symbols_dev, indexes_dev):
+        sym, idx = _to_host(symbols_dev), _to_host(indexes_dev)
+        cdf, length, offset = self._tables()
+        t0 = time.perf_counter()
+        s = ops.rans_encode(sym, idx, cdf, length, offset)
+        coder_stats["encode_s"] += time.perf_counter() - t0
+        coder_stats["symbols"] += sym.size
+        return s
+
+    def _decode(self, string, indexes_host):
+        cdf, length, offset = self._tables()
+        t0 = time.perf_counter()
+        out = ops.rans_decode(string, indexes_host, cdf, length, offset)
+        coder_stats["decode_s"] += time.perf_counter() - t0
+        coder_stats["symbols"] += out.size
+        return out
+
+
+class EntropyBottleneck(EntropyModel):
+    """compressai.entropy_models.EntropyBottleneck (SURVEY.md Appendix B1;
+    model/entropy_models.py:269,313,352-353,393)."""
+
+    def __init__(self, channels, *args, tail_mass=1e-9, init_scale=10, filters=(3, 3, 3, 3), **kwargs):
+        super().__init__(*args, **kwargs)
+        if tuple(filters) != (3, 3, 3, 3):
+            raise PccError("only the default filters (3,3,3,3) are supported")
+        self.channels = int(channels)
+        self.filters = tuple(int(f) for f in filters)
+        self.init_scale = float(init_scale)
+        self.tail_mass = float(tail_mass)
+        f = (1,) + self.filters + (1,)
+        scale = self.init_scale ** (1 / (len(self.filters) + 1))
+        for i in range(len(self.filters) + 1):
+            init = np.log(np.expm1(1 / scale / f[i + 1]))
+            matrix = torch.Tensor(channels, f[i + 1], f[i])
+            matrix.data.fill_(init)
+            self.register_parameter(f"_matrix{i:d}", nn.Parameter(matrix))
+            bias = torch.Tensor(channels, f[i + 1], 1)
+            nn.init.uniform_(bias, -0.5, 0.5)
+            self.register_parameter(f"_bias{i:d}", nn.Parameter(bias))
+            if i < len(self.filters):
+                factor = torch.Tensor(channels, f[i + 1], 1)
+                nn.init.zeros_(factor)
+                self.register_parameter(f"_factor{i:d}", nn.Parameter(factor))
+        self.quantiles = nn.Parameter(torch.Tensor(channels, 1, 3))
+        init = torch.Tensor([-self.init_scale, 0, self.init_scale])
+        self.quantiles.data = init.repeat(self.quantiles.size(0), 1, 1)
+        target = np.log(2 / self.tail_mass - 1)
+        self.register_buffer("target", torch.Tensor([-target, 0, target]))
+
+    # -- host-side table construction (one-off; ColorModel.update, model/model.py:30-36)
+    def update(self, force=False):
+        if self._offset.numel() > 0 and not force:
+            return False
+        g = lambda name: getattr(self, name).detach().cpu().numpy().astype(np.float32)
+        cdf, length, offset = ops.factorized_cdf_tables(
+            [g(f"_matrix{i}") for i in range(5)], [g(f"_bias{i}") for i in range(5)],
+            [g(f"_factor{i}") for i in range(4)], g("quantiles"))
+        self._set_tables(cdf, length, offset)
+        return True
+
+    def _device_params(self, device):
+        """medians [C] and the 58 pre-transformed floats per channel the likelihood kernel reads."""
+        key = str(device)
+        if key not in self._dev_cache:
+            with torch.no_grad():
+                parts = []
+                for i in range(5):
+                    parts.append(torch.nn.functional.softplus(getattr(self, f"_matrix{i}").double()).reshape(self.channels, -1))
+                    parts.append(getattr(self, f"_bias{i}").double().reshape(self.channels, -1))
+                    if i < 4:
+                        parts.append(torch.tanh(getattr(self, f"_factor{i}").double()).reshape(self.channels, -1))
+                packed = torch.cat(parts, dim=1).float().contiguous().to(device)
+                med = self.quantiles[:, 0, 1].detach().float().contiguous().to(device)
+            self._dev_cache[key] = (med, packed)
+        return self._dev_cache[key]
+
+    def _get_medians(self):
+        return self.quantiles[:, :, 1:2].detach()
+
+    def forward(self, x, training=None):
+        if training if training is not None else self.training:
+            raise PccError("training-mode (noise) quantisation is outside the encode/decode path")
+        z = _rows_cn(x)
+        med, packed = self._device_params(z.device)
+        z_hat, lik = ops.eb_likelihood(z, med, packed, self._likelihood_bound if self.use_likelihood_bound else 0.0)
+        return z_hat.t().unsqueeze(0), lik.unsqueeze(0)
+
+    def quantize_rows(self, z):
+        """z [N, C] -> (symbols [C, N] int32 device, z_hat [N, C])."""
+        med, _ = self._device_params(z.device)
+        return ops.eb_quantize(z, med)
+
+    def compress(self, x):
+        z = _rows_cn(x)
+        sym, _ = self.quantize_rows(z)
+        return [self.compress_symbols(sym)]
+
+    def compress_symbols(self, sym_dev):
+        c, n = sym_dev.shape
+        idx = np.repeat(np.arange(c, dtype=np.int32)[:, None], n, axis=1)
+        sym = _to_host(sym_dev)
+        cdf, length, offset = self._tables()
+        t0 = time.perf_counter()
+        s = ops.rans_encode(sym, idx, cdf, length, offset)
+        coder_stats["encode_s"] += time.perf_counter() - t0
+        coder_stats["symbols"] += sym.size
+        return s
+
+    def decompress(self, strings, size):
+        n = int(size[0]) if isinstance(size, (list, tuple, torch.Size)) else int(size)
+        device = self.quantiles.device
+        idx = np.repeat(np.arange(self.channels, dtype=np.int32)[:, None], n, axis=1)
+        sym = self._decode(strings[0], idx).reshape(self.channels, n)
+        med, _ = self._device_params(device)
+        z_hat = ops.eb_dequantize(_to_dev(sym, device), med)
+        return z_hat.t().unsqueeze(0)
+
+    def _logits_cumulative(self, inputs):
+        logits = inputs
+        for i in range(5):
+            logits = torch.matmul(torch.nn.functional.softplus(getattr(self, f"_matrix{i}")), logits)
+            logits = logits + getattr(self, f"_bias{i}")
+            if i < 4:
+                logits = logits + torch.tanh(getattr(self, f"_factor{i}")) * torch.tanh(logits)
+        return logits
+
+    def loss(self):
+        logits = self._logits_cumulative(self.quantiles.detach() if False else self.quantiles)
+        return torch.abs(logits - self.target).sum()
+
+
+class GaussianConditional(EntropyModel):
+    """compressai.entropy_models.GaussianConditional (SURVEY.md Appendix B2;
+    model/entropy_models.py:270,330,371-372,407-408)."""
+
+    def __init__(self, scale_table, *args, scale_bound=0.11, tail_mass=1e-9, **kwargs):
+        super().__init__(*args, **kwargs)
+        if scale_table is not None and (len(scale_table) < 1 or len(scale_table) > 64):
+            raise PccError("scale_table must have 1..64 entries")
+        self.tail_mass = float(tail_mass)
+        if scale_bound is None and scale_table:
+            scale_bound = float(scale_table[0])
+        self._scale_bound = float(scale_bound)
+        self.lower_bound_scale = LowerBound(scale_bound)
+        self.register_buffer("scale_table", torch.Tensor(tuple(float(s) for s in scale_table))
+                             if scale_table is not None else torch.Tensor())
+        self.register_buffer("scale_bound", torch.Tensor([float(scale_bound)]))
+
+    def update_scale_table(self, scale_table, force=False):
+        if self._offset.numel() > 0 and not force:
+            return False
+        dev = self.scale_table.device
+        self.scale_table = torch.as_tensor(scale_table, dtype=torch.float32).to(dev)
+        self.update()
+        return True
+
+    def update(self):
+        st = self.scale_table.detach().cpu().numpy().astype(np.float32)
+        cdf, length, offset = ops.gaussian_cdf_tables(st, self.tail_mass)
+        self._set_tables(cdf, length, offset)
+
+    def _table_dev(self, device):
+        key = str(device)
+        if key not in self._dev_cache:
+            self._dev_cache[key] = self.scale_table.detach().float().contiguous().to(device)
+        return self._dev_cache[key]
+
+    @staticmethod
+    def _params(scales, means):
+        s = _rows_cn(scales)
+        m = _rows_cn(means) if means is not None else torch.zeros_like(s)
+        return torch.cat([s, m], dim=1)
+
+    def build_indexes(self, scales):
+        s = _rows_cn(scales)
+        params = torch.cat([s, s], dim=1)
+        idx = ops.gc_build_indexes(params, None, s.shape[0], s.shape[1], self._table_dev(s.device), self._scale_bound)
+        return idx.unsqueeze(0)
+
+    def forward(self, inputs, scales, means=None, training=None):
+        if training if training is not None else self.training:
+            raise PccError("training-mode (noise) quantisation is outside the encode/decode path")
+        y = _rows_cn(inputs)
+        y_hat, lik = ops.gc_likelihood(y, self._params(scales, means), None, self._scale_bound,
+                                       self._likelihood_bound if self.use_likelihood_bound else 0.0)
+        return y_hat.t().unsqueeze(0), lik.unsqueeze(0)
+
+    def compress(self, inputs, indexes, means=None):
+        y = _rows_cn(inputs)
+        m = _rows_cn(means) if means is not None else torch.zeros_like(y)
+        sym, _ = ops.gc_quantize_index(y, torch.cat([m, m], dim=1), None, self._table_dev(y.device), self._scale_bound)
+        return [self._encode(sym, indexes[0].contiguous())]
+
+    def compress_fused(self, y, params, rows):
+        """Fused path: y [N, C], params [Np, 2C] (scales | means), rows [N] -> bytes."""
+        sym, idx = ops.gc_quantize_index(y, params, rows, self._table_dev(y.device), self._scale_bound)
+        return self._encode(sym, idx), sym, idx
+
+    def decompress(self, strings, indexes, dtype=torch.float, means=None):
+        idx_dev = indexes[0].contiguous()
+        sym = self._decode(strings[0], _to_host(idx_dev)).reshape(idx_dev.shape)
+        sym_dev = _to_dev(sym, idx_dev.device)
+        c, n = sym.shape
+        m = _rows_cn(means) if means is not None else torch.zeros((n, c), device=idx_dev.device)
+        y_hat = ops.gc_dequantize(sym_dev, torch.cat([m, m], dim=1), None)
+        return y_hat.t().unsqueeze(0)
+
+    def decompress_fused(self, string, params, rows, n, c):
+        """Fused path -> y_hat [N, C]."""
+        idx = ops.gc_build_indexes(params, rows, n, c, self._table_dev(params.device), self._scale_bound)
+        sym = self._decode(string, _to_host(idx)).reshape(c, n)
+        return ops.gc_dequantize(_to_dev(sym, params.device), params, rows)
+
+
+class CompressionModel(nn.Module):
+    """compressai.models.base.CompressionModel: update(force=) walks the entropy sub-modules,
+    aux_loss() sums the bottleneck losses (model/model.py:15,34,45)."""
+
+    def update(self, scale_table=None, force=False):
+        if scale_table is None:
+            scale_table = get_scale_table()
+        updated = False
+        for _, m in self.named_modules():
+            if isinstance(m, EntropyBottleneck):
+                updated |= m.update(force=force)
+            if isinstance(m, GaussianConditional):
+                updated |= m.update_scale_table(scale_table, force=force)
+        return updated
+
+    def aux_loss(self):
+        return sum(m.loss() for m in self.modules() if isinstance(m, EntropyBottleneck))

@@ -1,0 +1,501 @@
+"""Functional layer over the C-ABI (include/pcc_b200.h): torch tensors in, raw pointers out.
+
+torch is plumbing here (device memory, streams); every computation is a ``pcc_*`` call into
+libpcc_b200.so.  There is no CPU fallback: tensors must live on a CUDA device.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import ConvArgs, check
+
+TILE_M = 128
+ACT_NONE, ACT_RELU, ACT_LEAKY = 0, 1, 2
+MODE_EXACT, MODE_TF32 = 0, 1
+LEAKY_SLOPE = 0.01  # ME.MinkowskiLeakyReLU default
+
+_launches = 0  # kernels enqueued through this module (bench.py reports it as gpu_launches)
+
+
+def launches():
+    return _launches
+
+
+def _count(n=1):
+    global _launches
+    _launches += n
+
+
+def _L():
+    return _lib.load()
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    if t is None:
+        return None
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def _need_cuda(t, name="tensor"):
+    if not t.is_cuda:
+        raise _lib.PccError(f"{name} must be a CUDA tensor: the product path has no CPU fallback")
+
+
+def _ws(nbytes, device):
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
+# ---------------------------------------------------------------------------- coordinates
+def pack_coords(coords):
+    """[N,4] int32 (b,x,y,z) -> int64 tensor holding the uint64 keys.  Raises on out-of-range."""
+    _need_cuda(coords, "coords")
+    coords = coords.to(torch.int32).contiguous()
+    n = coords.shape[0]
+    keys = torch.empty(n, dtype=torch.int64, device=coords.device)
+    status = torch.zeros(1, dtype=torch.int32, device=coords.device)
+    check(_L().pcc_coords_pack(_ptr(coords), n, _ptr(keys), _ptr(status), _stream()), "pcc_coords_pack")
+    _count()
+    return keys, status
+
+
+def unpack_keys(keys):
+    n = keys.shape[0]
+    coords = torch.empty((n, 4), dtype=torch.int32, device=keys.device)
+    check(_L().pcc_coords_unpack(_ptr(keys), n, _ptr(coords), _stream()), "pcc_coords_unpack")
+    _count()
+    return coords
+
+
+def sort_keys(keys, want_perm=True):
+    """Canonical (lexicographic b,x,y,z) order.  Returns (sorted_keys, perm int32 or None)."""
+    n = keys.shape[0]
+    out = torch.empty_like(keys)
+    perm = torch.empty(n, dtype=torch.int32, device=keys.device) if want_perm else None
+    if n == 0:
+        return out, perm
+    wsb = _L().pcc_sort_ws_bytes(n)
+    ws = _ws(wsb, keys.device)
+    check(_L().pcc_sort_keys(_ptr(keys), n, _ptr(out), _ptr(perm), _ptr(ws), wsb, _stream()), "pcc_sort_keys")
+    _count(4)
+    return out, perm
+
+
+class KernelMap:
+    """nbr [K, stride] int32 (offset-major), tapmask [ceil(n_out/128)] uint32 (as int32)."""
+    __slots__ = ("nbr", "tapmask", "K", "n_out", "stride")
+
+    def __init__(self, nbr, tapmask, K, n_out, stride):
+        self.nbr, self.tapmask, self.K, self.n_out, self.stride = nbr, tapmask, K, n_out, stride
+
+
+class CoordMap:
+    """One coordinate map: unique keys in row order + (lazy) hash table + cached derived maps.
+
+    Plays the role of one entry of ME's coordinate manager; maps derived from it (stride-2
+    children, generative children, kernel maps) are cached on the object, which is what lets
+    layers that share coordinates share maps.
+    """
+
+    def __init__(self, keys, ts, is_sorted):
+        self.keys = keys
+        self.ts = int(ts)
+        self.is_sorted = bool(is_sorted)
+        self._hash = None
+        self._coords = None
+        self._derived = {}
+        self._kmaps = {}
+
+    @property
+    def n(self):
+        return self.keys.shape[0]
+
+    @property
+    def device(self):
+        return self.keys.device
+
+    @property
+    def coords(self):
+        if self._coords is None:
+            self._coords = unpack_keys(self.keys)
+        return self._coords
+
+    def hash(self):
+        if self._hash is None:
+            cap = _L().pcc_hash_capacity(self.n)
+            tkeys = torch.empty(cap, dtype=torch.int64, device=self.device)
+            tvals = torch.empty(cap, dtype=torch.int32, device=self.device)
+            check(_L().pcc_hash_build(_ptr(self.keys), self.n, _ptr(tkeys), _ptr(tvals), cap, _stream()),
+                  "pcc_hash_build")
+            _count(2)
+            self._hash = (tkeys, tvals, cap)
+        return self._hash
+
+    def lookup(self, q_keys):
+        """rows of q_keys in this map (-1 when absent)."""
+        nq = q_keys.shape[0]
+        rows = torch.empty(nq, dtype=torch.int32, device=self.device)
+        if nq:
+            tk, tv, cap = self.hash()
+            check(_L().pcc_hash_probe(_ptr(tk), _ptr(tv), cap, _ptr(q_keys), nq, _ptr(rows), _stream()),
+                  "pcc_hash_probe")
+            _count()
+        return rows
+
+    def stride2(self):
+        """Output map of a stride-2 convolution (sorted)."""
+        if "s2" not in self._derived:
+            n = self.n
+            out = torch.empty(max(n, 1), dtype=torch.int64, device=self.device)
+            n_out = ctypes.c_int64(0)
+            wsb = _L().pcc_stride_ws_bytes(n)
+            ws = _ws(wsb, self.device)
+            check(_L().pcc_coords_stride(_ptr(self.keys), n, self.ts * 2, _ptr(out), ctypes.byref(n_out),
+                                         _ptr(ws), wsb, _stream()), "pcc_coords_stride")
+            _count(8)
+            self._derived["s2"] = CoordMap(out[:n_out.value].clone() if n_out.value < n else out[:n_out.value],
+                                           self.ts * 2, True)
+        return self._derived["s2"]
+
+    def expand(self, kernel_size):
+        """Generative output map of a stride-2 transposed convolution (sorted)."""
+        key = ("ex", kernel_size)
+        if key not in self._derived:
+            n = self.n
+            K = kernel_size ** 3
+            out = torch.empty(max(n * K, 1), dtype=torch.int64, device=self.device)
+            n_out = ctypes.c_int64(0)
+            wsb = _L().pcc_expand_ws_bytes(n, kernel_size)
+            ws = _ws(wsb, self.device)
+            tk, tv, cap = self.hash()
+            check(_L().pcc_coords_expand(_ptr(tk), _ptr(tv), cap, _ptr(self.keys), n, kernel_size, self.ts,
+                                         _ptr(out), ctypes.byref(n_out), _ptr(ws), wsb, _stream()),
+                  "pcc_coords_expand")
+            _count(8)
+            self._derived[key] = CoordMap(out[:n_out.value].clone(), self.ts // 2, True)
+        return self._derived[key]
+
+    def kernel_map(self, out_map, kernel_size, transpose=False):
+        """Kernel map from this (input) map to out_map.  conv: targets c_o + d*ts_in;
+        transpose: targets q - d*ts_out, probed only when aligned to ts_in."""
+        key = (id(out_map), kernel_size, transpose)
+        km = self._kmaps.get(key)
+        if km is not None and km[0] is out_map:
+            return km[1]
+        K = kernel_size ** 3
+        n_out = out_map.n
+        stride = max(n_out, 1)
+        nbr = torch.empty((K, stride), dtype=torch.int32, device=self.device)
+        tapmask = torch.empty(max((n_out + TILE_M - 1) // TILE_M, 1), dtype=torch.int32, device=self.device)
+        if n_out:
+            tk, tv, cap = self.hash()
+            step = -out_map.ts if transpose else self.ts
+            align = self.ts if transpose else 1
+            check(_L().pcc_kernel_map(_ptr(tk), _ptr(tv), cap, _ptr(out_map.keys), n_out, kernel_size, step,
+                                      align, _ptr(nbr), stride, _ptr(tapmask), _stream()), "pcc_kernel_map")
+            _count()
+        kmap = KernelMap(nbr, tapmask, K, n_out, stride)
+        self._kmaps[key] = (out_map, kmap)
+        return kmap
+
+
+def make_map(coords_or_keys, ts=1, assume_sorted=False):
+    """CoordMap from [N,4] int coordinates (or packed keys), rows kept in the given order."""
+    if coords_or_keys.dim() == 2:
+        keys, status = pack_coords(coords_or_keys)
+        if int(status.item()) != 0:
+            raise _lib.PccError("coordinate out of the packable range (|x|,|y|,|z| < 32768, 0 <= b < 65536)")
+    else:
+        keys = coords_or_keys
+    return CoordMap(keys, ts, assume_sorted)
+
+
+def canonical_map(coords, ts=1):
+    """Sort coordinates into canonical order.  Returns (CoordMap sorted, perm int64) and checks
+    uniqueness (one host sync)."""
+    keys, status = pack_coords(coords)
+    skeys, perm = sort_keys(keys)
+    dup = (skeys[1:] == skeys[:-1]).any() if skeys.shape[0] > 1 else torch.zeros((), dtype=torch.bool, device=keys.device)
+    flags = torch.stack([status[0] != 0, dup.reshape(())]).tolist()
+    if flags[0]:
+        raise _lib.PccError("coordinate out of the packable range (|x|,|y|,|z| < 32768, 0 <= b < 65536)")
+    if flags[1]:
+        raise _lib.PccError("duplicate coordinates")
+    return CoordMap(skeys, ts, True), perm.long()
+
+
+# ---------------------------------------------------------------------------- convolution
+_default_mode = MODE_EXACT
+
+
+def set_default_mode(mode):
+    """PCC_MODE_EXACT (bit-exact vs oracle) or PCC_MODE_TF32 (tcgen05 where the layer allows)."""
+    global _default_mode
+    _default_mode = int(mode)
+
+
+def default_mode():
+    return _default_mode
+
+
+def tf32_eligible(cin, cout):
+    return cin % 32 == 0 and cout % 32 == 0 and 32 <= cout <= 256
+
+
+def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None, residual=None,
+         res_rows=None, out=None, mode=None):
+    """out[o] = epilogue(sum_k feats[nbr[k,o]] @ weight[k]).
+
+    weight: [K, cin, cout] (or [cin, cout] for K == 1), bias: [1, cout] or [cout].
+    film: [n_film, 2*cf] (beta | gamma), cf in {cout, 1}; residual: [n_res, cout].
+    """
+    _need_cuda(feats, "feats")
+    feats = feats.contiguous()
+    w = weight if weight.dim() == 3 else weight.unsqueeze(0)
+    w = w.contiguous()
+    K, cin, cout = w.shape
+    if K != kmap.K or feats.shape[1] != cin:
+        raise _lib.PccError(f"conv shape mismatch: feats {tuple(feats.shape)}, weight {tuple(w.shape)}, K {kmap.K}")
+    n_out = kmap.n_out
+    if out is None:
+        out = torch.empty((n_out, cout), dtype=torch.float32, device=feats.device)
+    if mode is None:
+        mode = _default_mode
+    if mode == MODE_TF32 and not tf32_eligible(cin, cout):
+        mode = MODE_EXACT  # stated policy: small-channel layers always run the exact CUDA-core path
+    a = ConvArgs()
+    a.in_ = feats.data_ptr()
+    a.n_in = feats.shape[0]
+    a.cin, a.cout = cin, cout
+    a.weight = w.data_ptr()
+    b = None if bias is None else bias.contiguous()
+    a.bias = None if b is None else b.data_ptr()
+    a.nbr = kmap.nbr.data_ptr()
+    a.nbr_stride = kmap.stride
+    a.tapmask = kmap.tapmask.data_ptr()
+    a.K = K
+    a.act = act
+    a.slope = LEAKY_SLOPE
+    keep = [feats, w, b]
+    if film is not None:
+        film = film.contiguous()
+        cf = film.shape[1] // 2
+        a.film_c = cf
+        a.film = film.data_ptr()
+        a.film_rows = None if film_rows is None else film_rows.data_ptr()
+        keep += [film, film_rows]
+    else:
+        a.film_c = 0
+    if residual is not None:
+        residual = residual.contiguous()
+        a.residual = residual.data_ptr()
+        a.res_rows = None if res_rows is None else res_rows.data_ptr()
+        keep += [residual, res_rows]
+    a.out = out.data_ptr()
+    a.n_out = n_out
+    a.out_stride = out.stride(0) if n_out else cout
+    a.mode = mode
+    check(_L().pcc_conv_fwd(ctypes.byref(a), _stream()), "pcc_conv_fwd")
+    if n_out:
+        _count()
+    return out
+
+
+def gather_rows(feats, rows, add=None):
+    """features_at_coordinates on-grid: out[i] = feats[rows[i]] (0 when rows[i] < 0) (+ add[i])."""
+    feats = feats.contiguous()
+    n = rows.shape[0] if rows is not None else feats.shape[0]
+    c = feats.shape[1]
+    out = torch.empty((n, c), dtype=torch.float32, device=feats.device)
+    if add is not None:
+        add = add.contiguous()
+    check(_L().pcc_gather_rows(_ptr(feats), c, _ptr(rows), n, _ptr(add), _ptr(out), _stream()), "pcc_gather_rows")
+    if n:
+        _count()
+    return out
+
+
+def take_keys(keys, rows):
+    out = torch.empty(rows.shape[0], dtype=torch.int64, device=keys.device)
+    check(_L().pcc_take_keys(_ptr(keys), _ptr(rows), rows.shape[0], _ptr(out), _stream()), "pcc_take_keys")
+    if rows.shape[0]:
+        _count()
+    return out
+
+
+def topk_rows(logits, k, column=0):
+    """Rows (ascending) of the k largest logits[:, column]; ties -> smaller row index."""
+    assert logits.dim() == 2
+    m = logits.shape[0]
+    k = int(k)
+    sel = torch.empty(k, dtype=torch.int32, device=logits.device)
+    wsb = _L().pcc_topk_ws_bytes(m)
+    ws = _ws(wsb, logits.device)
+    base = logits.data_ptr() + 4 * column * logits.stride(1)
+    check(_L().pcc_topk_select(ctypes.c_void_p(base), logits.stride(0), m, k, _ptr(sel), _ptr(ws), wsb, _stream()),
+          "pcc_topk_select")
+    if k:
+        _count(17)
+    return sel
+
+
+# ---------------------------------------------------------------------------- entropy stage
+def gc_quantize_index(y, params, rows, scale_table, scale_bound):
+    """-> symbols [C,N] int32, indexes [C,N] int32 (channel-major, what the coder consumes)."""
+    n, c = y.shape
+    sym = torch.empty((c, n), dtype=torch.int32, device=y.device)
+    idx = torch.empty((c, n), dtype=torch.int32, device=y.device)
+    check(_L().pcc_gc_quantize_index(_ptr(y.contiguous()), _ptr(params.contiguous()), _ptr(rows), n, c,
+                                     _ptr(scale_table), scale_table.shape[0], scale_bound, _ptr(sym), _ptr(idx),
+                                     _stream()), "pcc_gc_quantize_index")
+    _count()
+    return sym, idx
+
+
+def gc_build_indexes(params, rows, n, c, scale_table, scale_bound):
+    idx = torch.empty((c, n), dtype=torch.int32, device=params.device)
+    check(_L().pcc_gc_build_indexes(_ptr(params.contiguous()), _ptr(rows), n, c, _ptr(scale_table),
+                                    scale_table.shape[0], scale_bound, _ptr(idx), _stream()), "pcc_gc_build_indexes")
+    _count()
+    return idx
+
+
+def gc_dequantize(symbols, params, rows):
+    c, n = symbols.shape
+    y_hat = torch.empty((n, c), dtype=torch.float32, device=symbols.device)
+    check(_L().pcc_gc_dequantize(_ptr(symbols.contiguous()), _ptr(params.contiguous()), _ptr(rows), n, c,
+                                 _ptr(y_hat), _stream()), "pcc_gc_dequantize")
+    _count()
+    return y_hat
+
+
+def gc_likelihood(y, params, rows, scale_bound, lik_bound):
+    n, c = y.shape
+    y_hat = torch.empty((n, c), dtype=torch.float32, device=y.device)
+    lik = torch.empty((c, n), dtype=torch.float32, device=y.device)
+    check(_L().pcc_gc_likelihood(_ptr(y.contiguous()), _ptr(params.contiguous()), _ptr(rows), n, c, scale_bound,
+                                 lik_bound, _ptr(y_hat), _ptr(lik), _stream()), "pcc_gc_likelihood")
+    _count()
+    return y_hat, lik
+
+
+def eb_quantize(z, medians):
+    n, c = z.shape
+    sym = torch.empty((c, n), dtype=torch.int32, device=z.device)
+    z_hat = torch.empty((n, c), dtype=torch.float32, device=z.device)
+    check(_L().pcc_eb_quantize(_ptr(z.contiguous()), _ptr(medians), n, c, _ptr(sym), _ptr(z_hat), _stream()),
+          "pcc_eb_quantize")
+    _count()
+    return sym, z_hat
+
+
+def eb_dequantize(symbols, medians):
+    c, n = symbols.shape
+    z_hat = torch.empty((n, c), dtype=torch.float32, device=symbols.device)
+    check(_L().pcc_eb_dequantize(_ptr(symbols.contiguous()), _ptr(medians), n, c, _ptr(z_hat), _stream()),
+          "pcc_eb_dequantize")
+    _count()
+    return z_hat
+
+
+def eb_likelihood(z, medians, eb_params, lik_bound):
+    n, c = z.shape
+    z_hat = torch.empty((n, c), dtype=torch.float32, device=z.device)
+    lik = torch.empty((c, n), dtype=torch.float32, device=z.device)
+    check(_L().pcc_eb_likelihood(_ptr(z.contiguous()), _ptr(medians), _ptr(eb_params), n, c, lik_bound,
+                                 _ptr(z_hat), _ptr(lik), _stream()), "pcc_eb_likelihood")
+    _count()
+    return z_hat, lik
+
+
+def color_finalize(keys, feats):
+    n, c = feats.shape
+    out = torch.empty((n, 3 + c), dtype=torch.float32, device=feats.device)
+    check(_L().pcc_color_finalize(_ptr(keys), _ptr(feats.contiguous()), n, c, _ptr(out), _stream()),
+          "pcc_color_finalize")
+    _count()
+    return out
+
+
+# ---------------------------------------------------------------------------- host coder
+def _np_ptr(a):
+    return ctypes.c_void_p(a.ctypes.data)
+
+
+def rans_encode(symbols, indexes, cdf, cdf_length, offset):
+    """numpy int32 arrays (host) -> bytes.  The reference's sequential CPU coder."""
+    import numpy as np
+    symbols = np.ascontiguousarray(symbols, dtype=np.int32).reshape(-1)
+    indexes = np.ascontiguousarray(indexes, dtype=np.int32).reshape(-1)
+    n = symbols.shape[0]
+    cap = 4 * n + 64
+    while True:
+        out = np.empty(cap, dtype=np.uint8)
+        nb = _L().pcc_rans_encode_with_indexes(_np_ptr(symbols), _np_ptr(indexes), n, _np_ptr(cdf), cdf.shape[1],
+                                               _np_ptr(cdf_length), _np_ptr(offset), cdf.shape[0], _np_ptr(out), cap)
+        if nb == -4:  # PCC_ERR_CAPACITY
+            cap *= 4
+            continue
+        check(nb, "pcc_rans_encode_with_indexes")
+        return out[:nb].tobytes()
+
+
+def rans_decode(string, indexes, cdf, cdf_length, offset):
+    import numpy as np
+    indexes = np.ascontiguousarray(indexes, dtype=np.int32).reshape(-1)
+    enc = np.frombuffer(string, dtype=np.uint8)
+    out = np.empty(indexes.shape[0], dtype=np.int32)
+    check(_L().pcc_rans_decode_with_indexes(_np_ptr(enc), enc.shape[0], _np_ptr(indexes), indexes.shape[0],
+                                            _np_ptr(cdf), cdf.shape[1], _np_ptr(cdf_length), _np_ptr(offset),
+                                            cdf.shape[0], _np_ptr(out)), "pcc_rans_decode_with_indexes")
+    return out
+
+
+def pmf_to_quantized_cdf(pmf, precision=16):
+    import numpy as np
+    pmf = np.ascontiguousarray(pmf, dtype=np.float32)
+    cdf = np.empty(pmf.shape[0] + 1, dtype=np.uint32)
+    check(_L().pcc_pmf_to_quantized_cdf(_np_ptr(pmf), pmf.shape[0], precision, _np_ptr(cdf)),
+          "pcc_pmf_to_quantized_cdf")
+    return cdf.astype(np.int32)
+
+
+def gaussian_cdf_tables(scale_table, tail_mass=1e-9):
+    """-> (cdf [n, stride] int32, cdf_length [n], offset [n]) numpy (host)."""
+    import numpy as np
+    st = np.ascontiguousarray(scale_table, dtype=np.float32)
+    n = st.shape[0]
+    stride = ctypes.c_int32(0)
+    check(_L().pcc_gaussian_cdf_tables(_np_ptr(st), n, tail_mass, None, ctypes.byref(stride), None, None),
+          "pcc_gaussian_cdf_tables")
+    cdf = np.zeros((n, stride.value), dtype=np.int32)
+    length = np.zeros(n, dtype=np.int32)
+    offset = np.zeros(n, dtype=np.int32)
+    check(_L().pcc_gaussian_cdf_tables(_np_ptr(st), n, tail_mass, _np_ptr(cdf), ctypes.byref(stride),
+                                       _np_ptr(length), _np_ptr(offset)), "pcc_gaussian_cdf_tables")
+    return cdf, length, offset
+
+
+def factorized_cdf_tables(matrices, biases, factors, quantiles):
+    """matrices/biases: 5 numpy float32 arrays, factors: 4, quantiles [C,1,3] -> tables (host)."""
+    import numpy as np
+    ms = [np.ascontiguousarray(m, dtype=np.float32) for m in matrices]
+    bs = [np.ascontiguousarray(b, dtype=np.float32) for b in biases]
+    fs = [np.ascontiguousarray(f, dtype=np.float32) for f in factors]
+    q = np.ascontiguousarray(quantiles, dtype=np.float32).reshape(-1, 3)
+    c = q.shape[0]
+    arr = lambda xs: (ctypes.c_void_p * len(xs))(*[x.ctypes.data for x in xs])
+    pm, pb, pf = arr(ms), arr(bs), arr(fs)
+    stride = ctypes.c_int32(0)
+    check(_L().pcc_factorized_cdf_tables(pm, pb, pf, _np_ptr(q), c, None, ctypes.byref(stride), None, None),
+          "pcc_factorized_cdf_tables")
+    cdf = np.zeros((c, stride.value), dtype=np.int32)
+    length = np.zeros(c, dtype=np.int32)
+    offset = np.zeros(c, dtype=np.int32)
+    check(_L().pcc_factorized_cdf_tables(pm, pb, pf, _np_ptr(q), c, _np_ptr(cdf), ctypes.byref(stride),
+                                         _np_ptr(length), _np_ptr(offset)), "pcc_factorized_cdf_tables")
+    return cdf, length, offset
