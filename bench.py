@@ -1,0 +1,397 @@
+#!/usr/bin/env python
+"""Headline benchmark: encode+decode points/sec on a synthetic ~800k-point 10-bit frame
+(BASELINE.json metric; configs[1]: Ours.yaml architecture, random-init weights, shell radius 252
+-> 799,458 voxels, RGB, uniform quality map).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+  python bench.py --impl reference --gpus N --steps K ...  # CPU restatement of the reference path
+
+A step = ColorModel.compress + ColorModel.decompress of one frame (in-memory variant, path=None).
+N > 1 (torchrun): frames are independent, so each rank codes its own frame of the synthetic
+sequence (configs[3]) with no data-path collective: weak scaling, value = sum of points / max time.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "encode+decode points/sec, 800k-pt 10-bit frame"
+UNIT = "points/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default=os.environ.get("PCC_BENCH_MODE", "exact"), choices=["exact", "tf32"])
+    ap.add_argument("--radius", type=float, default=252.0, help="shell radius (252 -> 799,458 voxels)")
+    ap.add_argument("--cpu-radius", type=float, default=89.0, help="shell radius of the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--config", default="ours", choices=["ours", "ablation"])
+    ap.add_argument("--q", type=float, nargs=2, default=[0.5, 0.5], metavar=("Q_G", "Q_A"))
+    ap.add_argument("--dump-layers", default=None, help="write the per-layer conv timing table here")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi sampling DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                 "-i", str(self.gpu)], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            f = [v.strip() for v in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smax.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.path)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------ workload
+def make_model(cfg_name, device=None):
+    import pcc_b200
+    cfg = pcc_b200.OURS_CONFIG if cfg_name == "ours" else pcc_b200.ABLATION_CONFIG
+    model = pcc_b200.ColorModel(cfg)
+    pcc_b200.init_synthetic(model, 0)
+    model.eval()
+    if device is not None:
+        model.to(device)
+        model.update()
+    return model, cfg
+
+
+def frame_for(rank, step, world, radius):
+    """Rank-sharded synthetic sequence: rank r codes frames r, r + world, ... (frame-parallel)."""
+    import pcc_b200
+    if world == 1:
+        return pcc_b200.synthetic.shell_frame(radius, seed=0)
+    t = step * world + rank
+    import numpy as np
+    r = radius + 4.0 * np.sin(2.0 * np.pi * t / 300.0)
+    return pcc_b200.synthetic.shell_frame(r, seed=t)
+
+
+# ------------------------------------------------------------------------------ reference arm
+def run_reference(args, rank):
+    """The reference's own CPU implementation cannot be installed (MinkowskiEngine / CompressAI
+    absent), so this arm times the CPU restatement (oracle/, kind "port") with all host threads on
+    a bounded sample of the workload: the ~100k-point frame of configs[0]."""
+    if rank != 0:
+        return
+    import torch
+    import pcc_b200
+    from oracle import OracleCodec, prims
+    model, cfg = make_model(args.config)
+    oc = OracleCodec(pcc_b200.export_params(model), cfg)
+    x = pcc_b200.synthetic.shell_frame(args.cpu_radius, seed=0)
+    qc, qf = pcc_b200.synthetic.uniform_q_map(x, *args.q)
+    xn, qcn, qfn = x.numpy(), qc.numpy(), qf.numpy()
+    steps, warmup = max(1, args.steps), max(0, min(args.warmup, 1))  # bounded: ~10-20 s per step
+
+    def step():
+        s, sh, k, c = oc.compress(xn, qcn, qfn)
+        return oc.decompress(c, s, sh, k)
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / steps
+    value = xn.shape[0] / dt
+    cores = prims.num_threads()
+    sample = f"shell radius {args.cpu_radius:g} ({xn.shape[0]} points, configs[0]) per step, {steps} steps"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"Ours.yaml random-init, encode+decode, bounded sample: {sample}"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ------------------------------------------------------------------------------ our arm
+def conv_flops(r):
+    return 2.0 * r["pairs"] * r["cin"] * r["cout"]
+
+
+def conv_bytes(r):
+    """Algorithmic bytes of one sparse conv: features in/out once, kernel map, weights."""
+    return 4.0 * (r["n_in"] * r["cin"] + r["n_out"] * r["cout"]) + 4.0 * r["K"] * r["n_out"] \
+        + 4.0 * r["K"] * r["cin"] * r["cout"]
+
+
+def roofline_pass(model, x_dev, q_dev, peaks, clocks, dump=None):
+    """One extra (untimed) step with CUDA events around every pcc_conv_fwd launch on the launching
+    stream; the dominant kernel is the 128-wide sparse-conv kernel (all cin,cout >= 64 layers)."""
+    import pcc_b200
+    ops = pcc_b200.ops
+    ops.start_conv_profile()
+    s, sh, k, c = model.compress(x_dev, q_dev)
+    model.decompress(coordinates=c, strings=s, shape=sh, k=k)
+    recs = ops.stop_conv_profile()
+    if not recs:
+        return None, []
+    big = [r for r in recs if r["cin"] >= 64 and r["cout"] >= 64]
+    dom = big if big else recs
+    t_ms = sum(r["ms"] for r in dom)
+    fl = sum(conv_flops(r) for r in dom)
+    tf32 = any(r["mode"] == 1 for r in dom)
+    achieved = fl / (t_ms * 1e-3) / 1e12
+    if tf32:
+        peak = peaks.get("bf16_tflops", 1590.0) / 2.0
+        bound, src = "tensor", "tf32 dense = measured bf16 burst / 2 (MEASURED_PEAKS.json)" \
+            if "bf16_tflops" in peaks else "fallback 1590/2"
+    else:
+        mhz = clocks.get("sm_max_mhz") or peaks.get("sm_max_mhz", 1965.0)
+        peak = 148 * 128 * 2 * mhz * 1e6 / 1e12
+        bound, src = "fp32_fma", f"148 SM x 128 FMA x 2 x {mhz:g} MHz (no measured FP32 peak exists)"
+    roof = {"bound": bound, "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+            "traffic": None, "kernel": "conv_tf32_kernel" if tf32 else "conv_exact_kernel<128>",
+            "launches": len(dom), "avg_launch_ms": t_ms / len(dom), "peak_source": src,
+            "share_of_conv_time": t_ms / sum(r["ms"] for r in recs),
+            "hbm_gbs_algorithmic": sum(conv_bytes(r) for r in dom) / (t_ms * 1e-3) / 1e9}
+    if dump:
+        with open(dump, "w") as f:
+            f.write("cin,cout,K,n_in,n_out,pairs,mode,ms,tflops,alg_GBs\n")
+            for r in recs:
+                f.write(f'{r["cin"]},{r["cout"]},{r["K"]},{r["n_in"]},{r["n_out"]},{r["pairs"]},{r["mode"]},'
+                        f'{r["ms"]:.4f},{conv_flops(r) / (r["ms"] * 1e-3) / 1e12:.3f},'
+                        f'{conv_bytes(r) / (r["ms"] * 1e-3) / 1e9:.1f}\n')
+    return roof, recs
+
+
+def cpu_baseline(args, cfg_name):
+    """Oracle (kind "port") timed on the host cores on a bounded sample (rank 0, N=1 only)."""
+    import pcc_b200
+    from oracle import OracleCodec, prims
+    model, cfg = make_model(cfg_name)
+    oc = OracleCodec(pcc_b200.export_params(model), cfg)
+    x = pcc_b200.synthetic.shell_frame(args.cpu_radius, seed=0)
+    qc, qf = pcc_b200.synthetic.uniform_q_map(x, *args.q)
+    t0 = time.perf_counter()
+    s, sh, k, c = oc.compress(x.numpy(), qc.numpy(), qf.numpy())
+    oc.decompress(c, s, sh, k)
+    dt = time.perf_counter() - t0
+    return {"value": x.shape[0] / dt, "unit": UNIT, "cores": prims.num_threads(), "kind": "port",
+            "sample": f"one encode+decode of the shell radius {args.cpu_radius:g} frame ({x.shape[0]} points, "
+                      f"configs[0]), {dt:.1f} s"}
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import pcc_b200
+    from pcc_b200 import compressai_compat as cc
+    ops = pcc_b200.ops
+
+    dev = torch.device(f"cuda:{local_rank}")
+    torch.cuda.set_device(dev)
+    ops.set_default_mode(ops.MODE_TF32 if args.mode == "tf32" else ops.MODE_EXACT)
+    model, cfg = make_model(args.config, dev)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+
+    total = args.warmup + args.steps
+    frames = [frame_for(rank, s, world, args.radius) for s in range(total if world > 1 else 1)]
+    get = (lambda s: frames[s]) if world > 1 else (lambda s: frames[0])
+    qmaps = {}
+
+    def host_inputs(s):
+        x = get(s)
+        if id(x) not in qmaps:
+            qc, qf = pcc_b200.synthetic.uniform_q_map(x, *args.q)
+            qmaps[id(x)] = (x.pin_memory(), qc.pin_memory(), qf.pin_memory())
+        return qmaps[id(x)]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device(xd, qd):
+        s, sh, k, c = model.compress(xd, qd)
+        return model.decompress(coordinates=c, strings=s, shape=sh, k=k)
+
+    def step_e2e(xh, qch, qfh):
+        s, sh, k, c = model.compress(xh, (qch, qfh))            # H2D of the frame inside
+        c_host = c.cpu()                                          # latent coordinates leave the device
+        out = model.decompress(coordinates=c_host, strings=s, shape=sh, k=k)
+        return out.cpu(), c_host
+
+    # ---- device-resident timing (value)
+    dev_inputs = []
+    for s in range(total):
+        xh, qch, qfh = host_inputs(s)
+        if world > 1 or s == 0:
+            dev_inputs.append((xh.to(dev), (qch.to(dev), qfh.to(dev))))
+        else:
+            dev_inputs.append(dev_inputs[0])
+    for s in range(args.warmup):
+        step_device(*dev_inputs[s])
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    cc.reset_coder_stats()
+    l0 = ops.launches()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    npts = 0
+    for s in range(args.warmup, total):
+        out = step_device(*dev_inputs[s])
+        npts += out.shape[0]
+    ev1.record()
+    barrier()
+    t_dev = ev0.elapsed_time(ev1) * 1e-3
+    launches = ops.launches() - l0
+    coder = dict(cc.coder_stats)
+    clocks = sampler.stop() if rank == 0 else {}
+
+    # ---- end-to-end timing through the public API with host buffers (e2e)
+    for s in range(min(args.warmup, 1)):
+        step_e2e(*host_inputs(s))
+    barrier()
+    cc.reset_coder_stats()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    t0 = time.perf_counter()
+    h2d = d2h = 0
+    for s in range(args.warmup, total):
+        xh, qch, qfh = host_inputs(s)
+        out, c_host = step_e2e(xh, qch, qfh)
+        h2d += xh.numel() * 4 + qch.numel() * 4 + qfh.numel() * 4 + c_host.numel() * 4
+        d2h += out.numel() * 4 + c_host.numel() * 4
+    e1.record()
+    barrier()
+    t_e2e = max(e0.elapsed_time(e1) * 1e-3, time.perf_counter() - t0)
+    h2d += cc.coder_stats["h2d_bytes"]
+    d2h += cc.coder_stats["d2h_bytes"]
+
+    # ---- max over ranks
+    if world > 1:
+        t = torch.tensor([t_dev, t_e2e], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_dev, t_e2e = t.tolist()
+        n = torch.tensor([npts], device=dev, dtype=torch.float64)
+        dist.all_reduce(n, op=dist.ReduceOp.SUM)
+        npts_all = int(n.item())
+    else:
+        npts_all = npts
+    if rank != 0:
+        return
+
+    roof = None
+    if not args.no_roofline:
+        roof, _ = roofline_pass(model, *dev_inputs[0], peaks, clocks, args.dump_layers)
+    base = None
+    if world == 1 and not args.no_cpu_baseline:
+        base = cpu_baseline(args, args.config)
+
+    n_frame = get(0).shape[0]
+    line = {
+        "metric": METRIC, "value": npts_all / t_dev, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32" if args.mode == "exact" else "tf32",
+        "data": "synthetic",
+        "config": {"workload": f"Ours.yaml random-init ({args.config}), encode+decode of one synthetic 10-bit "
+                               f"voxelised shell frame, radius {args.radius:g} -> {n_frame} points, RGB, "
+                               f"uniform q=({args.q[0]:g},{args.q[1]:g}); in-memory variant (path=None)",
+                   "mode": args.mode, "frames_per_step_per_gpu": 1, "parallelism": f"frame-parallel x{world}",
+                   "l2": "per-step working set (>1 GB of activations and kernel maps) exceeds the 126 MB L2; no flush",
+                   "includes_cpu_range_coder": True},
+        "e2e": {"value": npts_all / t_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d // args.steps,
+                "d2h_bytes_per_step": d2h // args.steps, "ms_per_step": t_e2e / args.steps * 1e3},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "coder": {"encode_ms_per_step": coder["encode_s"] / args.steps * 1e3,
+                  "decode_ms_per_step": coder["decode_s"] / args.steps * 1e3,
+                  "copies_ms_per_step": (coder["d2h_s"] + coder["h2d_s"]) / args.steps * 1e3,
+                  "symbols_per_step": coder["symbols"] // args.steps,
+                  "note": "reference's sequential CPU rANS, inside ms_per_step; value_excl_coder removes it"},
+        "value_excl_coder": npts_all / max(t_dev - coder["encode_s"] - coder["decode_s"], 1e-9),
+    }
+    if roof is not None:
+        line["roofline"] = roof
+    if base is not None:
+        line["cpu_baseline"] = base
+    print(json.dumps(line))
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (the product path has no CPU fallback); "
+                         "use --impl reference for the CPU restatement")
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    try:
+        run_ours(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

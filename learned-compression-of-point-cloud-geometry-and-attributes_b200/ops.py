@@ -87,7 +87,7 @@ def sort_keys(keys, want_perm=True):
 
 class KernelMap:
     """nbr [K, stride] int32 (offset-major), tapmask [ceil(n_out/128)] uint32 (as int32)."""
-    __slots__ = ("nbr", "tapmask", "K", "n_out", "stride")
+    __slots__ = ("nbr", "tapmask", "K", "n_out", "stride", "_pairs_cache")
 
     def __init__(self, nbr, tapmask, K, n_out, stride):
         self.nbr, self.tapmask, self.K, self.n_out, self.stride = nbr, tapmask, K, n_out, stride
@@ -230,6 +230,32 @@ def canonical_map(coords, ts=1):
 
 # ---------------------------------------------------------------------------- convolution
 _default_mode = MODE_EXACT
+_profile = None  # list of per-launch records while conv profiling is on (bench.py roofline pass)
+
+
+def start_conv_profile():
+    """Record CUDA events (on the launching stream) around every pcc_conv_fwd launch."""
+    global _profile
+    _profile = []
+
+
+def stop_conv_profile():
+    """-> list of dicts: cin, cout, K, n_in, n_out, pairs, mode, ms (after a device sync)."""
+    global _profile
+    recs, _profile = _profile, None
+    torch.cuda.synchronize()
+    out = []
+    for r in recs or []:
+        r = dict(r)
+        r["ms"] = r.pop("ev0").elapsed_time(r.pop("ev1"))
+        out.append(r)
+    return out
+
+
+def _pairs(kmap):
+    if not hasattr(kmap, "_pairs_cache"):
+        kmap._pairs_cache = int((kmap.nbr[:, :kmap.n_out] >= 0).sum().item()) if kmap.n_out else 0
+    return kmap._pairs_cache
 
 
 def set_default_mode(mode):
@@ -299,6 +325,16 @@ def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None
     a.n_out = n_out
     a.out_stride = out.stride(0) if n_out else cout
     a.mode = mode
+    if _profile is not None and n_out:
+        rec = {"cin": cin, "cout": cout, "K": K, "n_in": int(feats.shape[0]), "n_out": int(n_out),
+               "pairs": _pairs(kmap), "mode": int(mode), "ev0": torch.cuda.Event(enable_timing=True),
+               "ev1": torch.cuda.Event(enable_timing=True)}
+        rec["ev0"].record()
+        check(_L().pcc_conv_fwd(ctypes.byref(a), _stream()), "pcc_conv_fwd")
+        rec["ev1"].record()
+        _profile.append(rec)
+        _count()
+        return out
     check(_L().pcc_conv_fwd(ctypes.byref(a), _stream()), "pcc_conv_fwd")
     if n_out:
         _count()

@@ -162,6 +162,7 @@ def test_likelihoods_tolerance(pcc, oracle):
     n, c = 700, 128
     model = pcc.ColorModel(pcc.OURS_CONFIG)
     pcc.codec.init_synthetic(model, 3)
+    model.eval()
     eb = model.entropy_model.entropy_bottleneck
     gcm = model.entropy_model.gaussian_conditional
     model.update()
