@@ -138,9 +138,12 @@ typedef struct pcc_conv_args {
   int64_t out_stride;       /* elements between output rows (>= cout) */
   int32_t mode;             /* PCC_MODE_* */
   int32_t reserved;
+  const float* weight_t;    /* [dev, K x cout x cin] (pcc_weight_transpose); required by PCC_MODE_TF32 */
 } pcc_conv_args;
 
 int pcc_conv_fwd(const pcc_conv_args* args, void* stream);
+/* One-off re-layout of a kernel for the tensor-core path: wt[k][co][ci] = w[k][ci][co]. */
+int pcc_weight_transpose(const float* w, int32_t K, int32_t cin, int32_t cout, float* wt, void* stream);
 
 /* SparseTensor.features_at_coordinates for on-grid queries == gather-or-zero
  * (sites listed at pcc_hash_probe).  out[i] = rows[i] >= 0 ? in[rows[i]] : 0, optionally

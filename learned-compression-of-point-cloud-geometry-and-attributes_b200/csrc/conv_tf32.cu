@@ -1,11 +1,385 @@
-// Sparse convolution forward, tcgen05 tensor-core mode (PCC_MODE_TF32).  Placeholder until the
-// UMMA kernel lands: reports "unsupported" so callers fail loudly instead of silently falling back.
+// Sparse convolution forward, tensor-core mode (PCC_MODE_TF32): tcgen05.mma kind::tf32 with the
+// fp32 accumulator in TMEM.
+//
+// Same output-stationary implicit GEMM as conv_exact.cu (one CTA = PCC_TILE_M = 128 output rows x
+// BN output channels; kernel offsets skipped through the tile's tap mask), but the contraction
+// runs on the 5th-generation tensor cores:
+//   * warps 0-3 (128 threads) gather: for every (offset k, 32-channel chunk) step they cp.async
+//     the 128 neighbour rows (zero-fill when missing) and the BN x 32 slice of the pre-transposed
+//     weights Wt[k][co][ci] into shared memory in the canonical K-major SWIZZLE_128B layout
+//     (8-row x 128-byte atoms, 16-byte chunk index XOR row%8), 4 stages deep.  A stage is
+//     published with  cp.async.wait_group -> fence.proxy.async -> mbarrier.arrive  (generic-proxy
+//     writes must be fenced before the tensor core's async-proxy reads);
+//   * warp 4, one elected lane, waits for the stage, issues 4 x tcgen05.mma (M=128, N=BN, K=8)
+//     and tcgen05.commit's the stage's "empty" mbarrier; after the last step it commits the
+//     accumulator barrier;
+//   * warps 0-3 then read their 32 TMEM lanes (tcgen05.ld 32x32b.x32), apply the fused epilogue
+//     (bias -> activation -> FiLM -> residual) and store.
+// Operands are fp32 bit patterns read as tf32 (low 13 mantissa bits ignored); products are exact,
+// accumulation is fp32 in TMEM.  Tolerance vs the exact mode is stated in tests/.
+//
+// Roofline: tensor pipe (tf32 dense) for cin, cout >= 64; the gather (128 B per row per step from
+// L2) is the competing bound, see DESIGN.md.
 #include "pcc_common.cuh"
 
 namespace pcc {
-bool conv_tf32_supported(const pcc_conv_args*) { return false; }
-int conv_tf32(const pcc_conv_args*, cudaStream_t) {
-  set_error("pcc_conv_fwd: PCC_MODE_TF32 kernel not built");
-  return PCC_ERR_INVALID_ARG;
+
+constexpr int TC_TM = PCC_TILE_M;      // 128 rows = UMMA M
+constexpr int TC_TK = 32;              // fp32 channels per stage = 128 bytes = one swizzle row
+constexpr int TC_STAGES = 4;          // = TC_LAG + 2: one stage being consumed, one published, two landing
+constexpr int TC_PRODUCERS = 128;      // warps 0-3
+constexpr int TC_THREADS = 160;        // + warp 4 (MMA issuer, TMEM allocator)
+constexpr int TC_LAG = 2;              // cp.async groups a producer thread keeps in flight
+
+struct TcParams {
+  const float* in;
+  const float* weight_t;  // [K][cout][cin]
+  const float* bias;
+  const int32_t* nbr;
+  const uint32_t* tapmask;
+  const float* film;
+  const int32_t* film_rows;
+  const float* residual;
+  const int32_t* res_rows;
+  float* out;
+  int64_t nbr_stride, n_out, out_stride;
+  int cin, cout, K, act, film_c;
+  float slope;
+};
+
+// ---------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void tc_cp_async16(uint32_t dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
+__device__ __forceinline__ void tc_cp_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tc_cp_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.shared::cta.b64 st, [%0];\n}\n" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      " .reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      " @p bra DONE;\n"
+      " bra WAIT_LOOP;\n"
+      "DONE:\n"
+      "}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(dst_smem), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      " .reg .pred p;\n"
+      " setp.ne.b32 p, %4, 0;\n"
+      " tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+// 32 lanes x 32 consecutive 32-bit columns -> 32 registers per thread (thread i <-> lane base+i)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+        "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+        "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (sm_100 encoding):
+//   [0,14) start address >> 4, [16,30) leading byte offset >> 4 (unused for swizzled K-major),
+//   [32,46) stride byte offset >> 4 (1024 B between 8-row atoms), [46,48) version = 1,
+//   [61,64) layout type = 2 (SWIZZLE_128B)
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)(1024u >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+// instruction descriptor, kind::tf32: D = f32 (bits 4-5 = 1), A = B = tf32 (format 2 at bits 7-9,
+// 10-12), both K-major, N >> 3 at [17,23), M >> 4 at [24,29)
+__host__ __device__ constexpr uint32_t make_idesc_tf32(int m, int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+// byte offset of (row, 16-byte chunk) inside a [rows x 128 B] SWIZZLE_128B K-major tile
+__device__ __forceinline__ uint32_t sw128_offset(int row, int chunk) {
+  return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) << 4));
+}
+
+template <int BN>
+struct TcSmem {
+  static constexpr int A_BYTES = TC_TM * 128;
+  static constexpr int B_BYTES = BN * 128;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int BAR_OFFSET = TC_STAGES * STAGE_BYTES;
+  static constexpr int TOTAL = BAR_OFFSET + 128 + 1024;  // + barriers/tmem slot + alignment slack
+};
+
+template <int BN>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+conv_tf32_kernel(const TcParams p) {
+  extern __shared__ unsigned char smem_raw[];
+  // 1024-byte alignment for the swizzle atoms
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  unsigned char* sbase = smem_raw + (base - raw);
+  using S = TcSmem<BN>;
+  const uint32_t bar_base = base + S::BAR_OFFSET;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (TC_STAGES + s); };
+  const uint32_t accum_bar = bar_base + 8u * (2 * TC_STAGES);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * TC_STAGES + 1);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(sbase + S::BAR_OFFSET + 8 * (2 * TC_STAGES + 1));
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int64_t tile_base = (int64_t)blockIdx.x * TC_TM;
+  const int co_base = blockIdx.y * BN;
+  const int nchunks = p.cin / TC_TK;
+  const uint32_t kfull = p.K >= 32 ? 0xffffffffu : ((1u << p.K) - 1u);
+  const uint32_t mask = p.tapmask ? (p.tapmask[blockIdx.x] & kfull) : kfull;
+  const int nsteps = __popc(mask) * nchunks;
+  constexpr uint32_t TMEM_COLS = BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256));
+
+  if (tid == 0) {
+    for (int s = 0; s < TC_STAGES; ++s) {
+      mbar_init(full_bar(s), TC_PRODUCERS);
+      mbar_init(empty_bar(s), 1);
+    }
+    mbar_init(accum_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  if (warp == 4) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_acc = *tmem_slot_ptr;
+
+  if (warp < 4) {
+    // ============================ producers: gather A rows, load B slice ============================
+    const int chunk = tid & 7;   // 16-byte chunk inside the 128-byte row
+    const int rbase = tid >> 3;  // rows rbase + 16 j
+    uint32_t pmask = mask;
+    int pk = pmask ? (__ffs(pmask) - 1) : 0;
+    int pchunk = 0;
+    int idx[8];
+    bool need_idx = true;
+    for (int s = 0; s < nsteps; ++s) {
+      const int stage = s % TC_STAGES;
+      if (s >= TC_STAGES) mbar_wait(empty_bar(stage), (uint32_t)(((s / TC_STAGES) - 1) & 1));
+      if (need_idx) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int64_t o = tile_base + rbase + 16 * j;
+          idx[j] = (o < p.n_out) ? __ldg(p.nbr + (int64_t)pk * p.nbr_stride + o) : -1;
+        }
+        need_idx = false;
+      }
+      const uint32_t a_stage = base + stage * S::STAGE_BYTES;
+      const uint32_t b_stage = a_stage + S::A_BYTES;
+      const int ci = pchunk * TC_TK + chunk * 4;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int r = rbase + 16 * j;
+        const bool ok = idx[j] >= 0;
+        const float* src = ok ? p.in + (int64_t)idx[j] * p.cin + ci : p.in;
+        tc_cp_async16(a_stage + sw128_offset(r, chunk), src, ok ? 16 : 0);
+      }
+      const float* wk = p.weight_t + ((int64_t)pk * p.cout + co_base) * p.cin + ci;
+#pragma unroll
+      for (int j = 0; j < BN / 16; ++j) {
+        const int r = rbase + 16 * j;  // weight row = output channel co_base + r
+        const bool ok = co_base + r < p.cout;
+        const float* src = ok ? wk + (int64_t)r * p.cin : p.weight_t;
+        tc_cp_async16(b_stage + sw128_offset(r, chunk), src, ok ? 16 : 0);
+      }
+      tc_cp_commit();
+      if (s >= TC_LAG) {
+        tc_cp_wait<TC_LAG>();
+        fence_proxy_async();
+        mbar_arrive(full_bar((s - TC_LAG) % TC_STAGES));
+      }
+      if (++pchunk == nchunks) {
+        pchunk = 0;
+        pmask &= pmask - 1;
+        pk = pmask ? (__ffs(pmask) - 1) : 0;
+        need_idx = true;
+      }
+    }
+    // drain: publish the last min(LAG, nsteps) stages
+    tc_cp_wait<0>();
+    fence_proxy_async();
+    for (int s = (nsteps > TC_LAG ? nsteps - TC_LAG : 0); s < nsteps; ++s) mbar_arrive(full_bar(s % TC_STAGES));
+  } else {
+    // ============================ MMA issuer (one elected lane) ============================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_tf32(TC_TM, BN);
+      for (int s = 0; s < nsteps; ++s) {
+        const int stage = s % TC_STAGES;
+        mbar_wait(full_bar(stage), (uint32_t)((s / TC_STAGES) & 1));
+        tc_fence_after();
+        const uint32_t a_stage = base + stage * S::STAGE_BYTES;
+        const uint32_t b_stage = a_stage + S::A_BYTES;
+#pragma unroll
+        for (int kk = 0; kk < TC_TK / 8; ++kk) {
+          const uint64_t da = make_sw128_desc(a_stage + kk * 32);
+          const uint64_t db = make_sw128_desc(b_stage + kk * 32);
+          umma_tf32(tmem_acc, da, db, idesc, (s > 0 || kk > 0) ? 1u : 0u);
+        }
+        umma_commit(empty_bar(stage));  // frees the smem stage when these MMAs retire
+      }
+      umma_commit(accum_bar);           // accumulator complete
+    }
+    __syncwarp();
+  }
+
+  // ============================ epilogue (warps 0-3 own TMEM lanes 32w .. 32w+31) ============================
+  if (warp < 4) {
+    if (nsteps > 0) {
+      mbar_wait(accum_bar, 0);
+      tc_fence_after();
+    }
+    const int64_t o = tile_base + warp * 32 + lane;
+    const bool live = o < p.n_out;
+    int64_t frow = o, rrow = o;
+    if (live && p.film_c && p.film_rows) frow = __ldg(p.film_rows + o);
+    if (live && p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
+    const bool vec4 = (p.out_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32) {
+      if (co_base + c0 >= p.cout) break;  // warp-uniform
+      uint32_t v[32];
+      if (nsteps > 0) {
+        tmem_ld32(tmem_acc + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = 0u;
+      }
+      if (live) {
+        float r[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const int col = co_base + c0 + i;
+          float x = __uint_as_float(v[i]);
+          if (col < p.cout) {
+            if (p.bias) x = __fadd_rn(x, __ldg(p.bias + col));
+            if (p.act == PCC_ACT_RELU)
+              x = fmaxf(x, 0.0f);
+            else if (p.act == PCC_ACT_LEAKY)
+              x = x > 0.0f ? x : __fmul_rn(x, p.slope);
+            if (p.film_c) {
+              float beta = 0.0f, gamma = 0.0f;
+              if (frow >= 0) {
+                const int fc = p.film_c == 1 ? 0 : col;
+                beta = __ldg(p.film + frow * 2 * p.film_c + fc);
+                gamma = __ldg(p.film + frow * 2 * p.film_c + p.film_c + fc);
+              }
+              x = __fadd_rn(__fmul_rn(x, beta), gamma);
+            }
+            if (p.residual) x = __fadd_rn(x, rrow >= 0 ? __ldg(p.residual + rrow * p.cout + col) : 0.0f);
+          }
+          r[i] = x;
+        }
+        float* dst = p.out + o * p.out_stride + co_base + c0;
+        if (vec4 && co_base + c0 + 32 <= p.cout) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 4)
+            *reinterpret_cast<float4*>(dst + i) = make_float4(r[i], r[i + 1], r[i + 2], r[i + 3]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (co_base + c0 + i < p.cout) dst[i] = r[i];
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) tmem_dealloc(tmem_acc, TMEM_COLS);
+}
+
+template <int BN>
+static int launch_tc(const TcParams& p, cudaStream_t st) {
+  const size_t smem = TcSmem<BN>::TOTAL;
+  PCC_CHECK_CUDA(cudaFuncSetAttribute(conv_tf32_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid((unsigned)ceil_div(p.n_out, TC_TM), (unsigned)ceil_div(p.cout, BN));
+  conv_tf32_kernel<BN><<<grid, TC_THREADS, smem, st>>>(p);
+  PCC_CHECK_LAUNCH("conv_tf32_kernel");
+  return PCC_OK;
+}
+
+bool conv_tf32_supported(const pcc_conv_args* a) {
+  return a->cin % 32 == 0 && a->cout % 32 == 0 && a->cout >= 32 && a->cout <= 256 && a->weight_t != nullptr &&
+         (reinterpret_cast<uintptr_t>(a->in) & 15) == 0 && (reinterpret_cast<uintptr_t>(a->weight_t) & 15) == 0;
+}
+
+int conv_tf32(const pcc_conv_args* a, cudaStream_t st) {
+  TcParams p;
+  p.in = a->in; p.weight_t = a->weight_t; p.bias = a->bias; p.nbr = a->nbr; p.tapmask = a->tapmask;
+  p.film = a->film; p.film_rows = a->film_rows; p.residual = a->residual; p.res_rows = a->res_rows;
+  p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
+  p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope;
+  if (a->cout % 128 == 0 || a->cout > 128) return launch_tc<128>(p, st);
+  if (a->cout > 64) return launch_tc<128>(p, st);
+  if (a->cout > 32) return launch_tc<64>(p, st);
+  return launch_tc<32>(p, st);
+}
+
+// wt[k][co][ci] = w[k][ci][co]
+__global__ void weight_transpose_kernel(const float* __restrict__ w, int K, int cin, int cout,
+                                        float* __restrict__ wt) {
+  __shared__ float tile[32][33];
+  const int k = blockIdx.z;
+  const int ci0 = blockIdx.y * 32, co0 = blockIdx.x * 32;
+  const float* wk = w + (int64_t)k * cin * cout;
+  float* wtk = wt + (int64_t)k * cin * cout;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int ci = ci0 + r, co = co0 + threadIdx.x;
+    tile[r][threadIdx.x] = (ci < cin && co < cout) ? wk[(int64_t)ci * cout + co] : 0.f;
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int co = co0 + r, ci = ci0 + threadIdx.x;
+    if (co < cout && ci < cin) wtk[(int64_t)co * cin + ci] = tile[threadIdx.x][r];
+  }
+}
+
 }  // namespace pcc
+
+extern "C" int pcc_weight_transpose(const float* w, int32_t K, int32_t cin, int32_t cout, float* wt, void* stream) {
+  PCC_REQUIRE(w && wt && K > 0 && cin > 0 && cout > 0, "bad argument");
+  dim3 grid((unsigned)pcc::ceil_div(cout, 32), (unsigned)pcc::ceil_div(cin, 32), (unsigned)K);
+  pcc::weight_transpose_kernel<<<grid, dim3(32, 8), 0, (cudaStream_t)stream>>>(w, K, cin, cout, wt);
+  PCC_CHECK_LAUNCH("weight_transpose_kernel");
+  return PCC_OK;
+}

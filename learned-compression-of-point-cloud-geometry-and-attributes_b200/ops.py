@@ -272,6 +272,25 @@ def tf32_eligible(cin, cout):
     return cin % 32 == 0 and cout % 32 == 0 and 32 <= cout <= 256
 
 
+_wt_cache = {}
+
+
+def transposed_weight(w):
+    """[K, cin, cout] -> cached [K, cout, cin] copy for the tensor-core path (pcc_weight_transpose),
+    rebuilt when the parameter is modified in place or re-allocated."""
+    key = w.data_ptr()
+    ver = (w._version, tuple(w.shape), str(w.device))
+    hit = _wt_cache.get(key)
+    if hit is not None and hit[0] == ver:
+        return hit[1]
+    K, cin, cout = w.shape
+    wt = torch.empty((K, cout, cin), dtype=torch.float32, device=w.device)
+    check(_L().pcc_weight_transpose(_ptr(w), K, cin, cout, _ptr(wt), _stream()), "pcc_weight_transpose")
+    _count()
+    _wt_cache[key] = (ver, wt)
+    return wt
+
+
 def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None, residual=None,
          res_rows=None, out=None, mode=None):
     """out[o] = epilogue(sum_k feats[nbr[k,o]] @ weight[k]).
@@ -298,6 +317,8 @@ def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None
     a.n_in = feats.shape[0]
     a.cin, a.cout = cin, cout
     a.weight = w.data_ptr()
+    wt = transposed_weight(w.detach()) if mode == MODE_TF32 else None
+    a.weight_t = None if wt is None else wt.data_ptr()
     b = None if bias is None else bias.contiguous()
     a.bias = None if b is None else b.data_ptr()
     a.nbr = kmap.nbr.data_ptr()
