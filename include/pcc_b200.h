@@ -115,6 +115,11 @@ int pcc_kernel_map(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, con
 #define PCC_MODE_EXACT 0 /* fp32 FFMA, k-major / ci-minor order: bit-identical to the oracle */
 #define PCC_MODE_TF32 1  /* tcgen05.mma kind::tf32, fp32 accumulate in TMEM (cin, cout % 32 == 0) */
 
+/* Store the outputs rounded to tf32 (round-to-nearest-away, cvt.rna.tf32.f32).  The tensor core
+ * truncates fp32 operands to tf32, which biases every product towards zero; when the producer has
+ * already rounded to nearest, the truncation is a no-op and the error stays unbiased. */
+#define PCC_CONV_ROUND_OUT_TF32 1
+
 typedef struct pcc_conv_args {
   const float* in;          /* [dev, n_in x cin] */
   int64_t n_in;
@@ -137,12 +142,12 @@ typedef struct pcc_conv_args {
   int64_t n_out;
   int64_t out_stride;       /* elements between output rows (>= cout) */
   int32_t mode;             /* PCC_MODE_* */
-  int32_t reserved;
+  int32_t flags;            /* PCC_CONV_* bit set */
   const float* weight_t;    /* [dev, K x cout x cin] (pcc_weight_transpose); required by PCC_MODE_TF32 */
 } pcc_conv_args;
 
 int pcc_conv_fwd(const pcc_conv_args* args, void* stream);
-/* One-off re-layout of a kernel for the tensor-core path: wt[k][co][ci] = w[k][ci][co]. */
+/* One-off re-layout of a kernel for the tensor-core path: wt[k][co][ci] = tf32_round(w[k][ci][co]). */
 int pcc_weight_transpose(const float* w, int32_t K, int32_t cin, int32_t cout, float* wt, void* stream);
 
 /* SparseTensor.features_at_coordinates for on-grid queries == gather-or-zero

@@ -27,7 +27,7 @@ class ConvArgs(ctypes.Structure):
         ("weight", P), ("bias", P), ("nbr", P), ("nbr_stride", I64), ("tapmask", P),
         ("K", I32), ("act", I32), ("slope", F32), ("film_c", I32),
         ("film", P), ("film_rows", P), ("residual", P), ("res_rows", P),
-        ("out", P), ("n_out", I64), ("out_stride", I64), ("mode", I32), ("reserved", I32),
+        ("out", P), ("n_out", I64), ("out_stride", I64), ("mode", I32), ("flags", I32),
         ("weight_t", P),
     ]
 

@@ -42,7 +42,7 @@ struct ConvParams {
   const int32_t* res_rows;
   float* out;
   int64_t nbr_stride, n_out, out_stride;
-  int cin, cout, K, act, film_c;
+  int cin, cout, K, act, film_c, flags;
   float slope;
 };
 
@@ -221,6 +221,7 @@ conv_exact_kernel(const ConvParams p) {
         const float r = rrow >= 0 ? __ldg(p.residual + rrow * p.cout + col) : 0.0f;
         v = __fadd_rn(v, r);
       }
+      if (p.flags & PCC_CONV_ROUND_OUT_TF32) v = round_tf32(v);
       p.out[o * p.out_stride + col] = v;
     }
   }
@@ -251,7 +252,7 @@ int conv_exact(const pcc_conv_args* a, cudaStream_t st) {
   p.in = a->in; p.weight = a->weight; p.bias = a->bias; p.nbr = a->nbr; p.tapmask = a->tapmask;
   p.film = a->film; p.film_rows = a->film_rows; p.residual = a->residual; p.res_rows = a->res_rows;
   p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
-  p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope;
+  p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope; p.flags = a->flags;
   if (a->cout > 64) return launch_exact<128>(p, st);
   if (a->cout > 32) return launch_exact<64>(p, st);
   if (a->cout > 16) return launch_exact<32>(p, st);

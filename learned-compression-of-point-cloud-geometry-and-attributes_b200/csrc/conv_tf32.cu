@@ -43,7 +43,7 @@ struct TcParams {
   const int32_t* res_rows;
   float* out;
   int64_t nbr_stride, n_out, out_stride;
-  int cin, cout, K, act, film_c;
+  int cin, cout, K, act, film_c, flags;
   float slope;
 };
 
@@ -307,6 +307,7 @@ conv_tf32_kernel(const TcParams p) {
               x = __fadd_rn(__fmul_rn(x, beta), gamma);
             }
             if (p.residual) x = __fadd_rn(x, rrow >= 0 ? __ldg(p.residual + rrow * p.cout + col) : 0.0f);
+            if (p.flags & PCC_CONV_ROUND_OUT_TF32) x = round_tf32(x);
           }
           r[i] = x;
         }
@@ -348,14 +349,14 @@ int conv_tf32(const pcc_conv_args* a, cudaStream_t st) {
   p.in = a->in; p.weight_t = a->weight_t; p.bias = a->bias; p.nbr = a->nbr; p.tapmask = a->tapmask;
   p.film = a->film; p.film_rows = a->film_rows; p.residual = a->residual; p.res_rows = a->res_rows;
   p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
-  p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope;
+  p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope; p.flags = a->flags;
   if (a->cout % 128 == 0 || a->cout > 128) return launch_tc<128>(p, st);
   if (a->cout > 64) return launch_tc<128>(p, st);
   if (a->cout > 32) return launch_tc<64>(p, st);
   return launch_tc<32>(p, st);
 }
 
-// wt[k][co][ci] = w[k][ci][co]
+// wt[k][co][ci] = tf32_round(w[k][ci][co])  (the tensor core would otherwise truncate)
 __global__ void weight_transpose_kernel(const float* __restrict__ w, int K, int cin, int cout,
                                         float* __restrict__ wt) {
   __shared__ float tile[32][33];
@@ -365,7 +366,7 @@ __global__ void weight_transpose_kernel(const float* __restrict__ w, int K, int 
   float* wtk = wt + (int64_t)k * cin * cout;
   for (int r = threadIdx.y; r < 32; r += blockDim.y) {
     const int ci = ci0 + r, co = co0 + threadIdx.x;
-    tile[r][threadIdx.x] = (ci < cin && co < cout) ? wk[(int64_t)ci * cout + co] : 0.f;
+    tile[r][threadIdx.x] = (ci < cin && co < cout) ? round_tf32(wk[(int64_t)ci * cout + co]) : 0.f;
   }
   __syncthreads();
   for (int r = threadIdx.y; r < 32; r += blockDim.y) {

@@ -34,22 +34,72 @@ struct Table {
   int32_t offset;
 };
 
-// Encoder state writing words backwards into [begin, end)
+// Per-(table, slot) encoder constants: ryg_rans Rans64EncSymbolInit.  x / freq is replaced by a
+// 64x64->128 multiply with a rounded-up reciprocal; the result is bit-identical to the division
+// form (that is the construction's guarantee), so the bitstream does not change.
+struct EncSym {
+  uint64_t x_max;
+  uint64_t rcp_freq;
+  uint32_t bias;
+  uint32_t cmpl_freq;
+  uint32_t rcp_shift;
+  uint32_t freq;
+};
+
+inline EncSym make_enc_sym(uint32_t start, uint32_t freq) {
+  EncSym s;
+  s.freq = freq;
+  s.x_max = ((kRansL >> kPrecision) << 32) * (uint64_t)freq;
+  s.cmpl_freq = (1u << kPrecision) - freq;
+  if (freq < 2) {
+    s.rcp_freq = ~0ull;
+    s.rcp_shift = 0;
+    s.bias = start + (1u << kPrecision) - 1;
+  } else {
+    uint32_t shift = 0;
+    while (freq > (1u << shift)) shift++;
+    uint64_t x0 = freq - 1;
+    const uint64_t x1 = 1ull << (shift + 31);
+    const uint64_t t1 = x1 / freq;
+    x0 += (x1 % freq) << 32;
+    const uint64_t t0 = x0 / freq;
+    s.rcp_freq = t0 + (t1 << 32);
+    s.rcp_shift = shift - 1;
+    s.bias = start;
+  }
+  return s;
+}
+
+// Encoder state writing 32-bit words back to front into a buffer that grows at the front.
 struct BackWriter {
-  uint32_t* ptr;
+  std::vector<uint32_t> buf;
+  size_t pos;  // index of the first written word
   uint64_t x;
-  inline void renorm(uint64_t x_max) {
-    if (x >= x_max) {
-      *--ptr = (uint32_t)x;
+  explicit BackWriter(size_t words) : buf(words), pos(words), x(kRansL) {}
+  inline void emit(uint32_t w) {
+    if (pos == 0) {
+      const size_t old = buf.size();
+      std::vector<uint32_t> nb(old * 2);
+      memcpy(nb.data() + old, buf.data(), old * sizeof(uint32_t));
+      buf.swap(nb);
+      pos = old;
+    }
+    buf[--pos] = w;
+  }
+  inline void put(const EncSym& s) {
+    if (x >= s.x_max) {
+      emit((uint32_t)x);
       x >>= 32;
     }
-  }
-  inline void put(uint32_t start, uint32_t freq) {
-    renorm(((kRansL >> kPrecision) << 32) * freq);
-    x = ((x / freq) << kPrecision) + (x % freq) + start;
+    const uint64_t q = (uint64_t)(((unsigned __int128)x * s.rcp_freq) >> 64) >> s.rcp_shift;
+    x = x + s.bias + q * s.cmpl_freq;
   }
   inline void put_bits(uint32_t val) {
-    renorm(((kRansL >> 16) << 32) * (uint64_t)(1u << (16 - kBypassBits)));
+    const uint64_t x_max = ((kRansL >> 16) << 32) * (uint64_t)(1u << (16 - kBypassBits));
+    if (x >= x_max) {
+      emit((uint32_t)x);
+      x >>= 32;
+    }
     x = (x << kBypassBits) | val;
   }
 };
@@ -131,61 +181,55 @@ int64_t pcc_rans_encode_with_indexes(const int32_t* symbols, const int32_t* inde
                                      const int32_t* cdfs, int32_t cdf_stride, const int32_t* cdf_sizes,
                                      const int32_t* offsets, int32_t n_tables, uint8_t* out,
                                      int64_t out_cap) {
-  if (n < 0 || (n > 0 && (!symbols || !indexes)) || !cdfs || !cdf_sizes || !offsets || !out) {
-    pcc::set_error("pcc_rans_encode_with_indexes: null pointer");
+  if (n < 0 || (n > 0 && (!symbols || !indexes)) || !cdfs || !cdf_sizes || !offsets || !out || n_tables <= 0) {
+    pcc::set_error("pcc_rans_encode_with_indexes: bad argument");
     return PCC_ERR_INVALID_ARG;
   }
-  // pass 1: count coder operations to size the back-to-front word buffer
-  int64_t ops = 0;
-  for (int64_t i = 0; i < n; ++i) {
+  // encoder constants per table, built on first use
+  std::vector<std::vector<EncSym>> enc((size_t)n_tables);
+  BackWriter w((size_t)n / 2 + 1024);
+  // Symbols are consumed in reverse.  Inside one symbol the reference pushed
+  //   [table symbol][count digits ...][nibbles low-first]
+  // so in reverse: nibbles high-first, count digits last-first, then the table symbol.
+  for (int64_t i = n - 1; i >= 0; --i) {
     const int32_t idx = indexes[i];
     if (idx < 0 || idx >= n_tables) {
       pcc::set_error("pcc_rans_encode_with_indexes: index %d out of range at %lld", idx, (long long)i);
       return PCC_ERR_INVALID_ARG;
     }
     const Table t{cdfs + (int64_t)idx * cdf_stride, cdf_sizes[idx] - 2, offsets[idx]};
-    int32_t slot;
-    uint32_t raw;
-    ops += 1;
-    if (classify(symbols[i], t, slot, raw)) {
-      const int nb = nibbles_of(raw);
-      ops += nb / kMaxBypass + 1 + nb;
+    std::vector<EncSym>& es = enc[idx];
+    if (es.empty()) {
+      es.resize((size_t)t.max_value + 1);
+      for (int32_t v = 0; v <= t.max_value; ++v) {
+        const int32_t f = t.cdf[v + 1] - t.cdf[v];
+        if (f <= 0) {
+          pcc::set_error("pcc_rans_encode_with_indexes: table %d has a non-positive frequency", idx);
+          return PCC_ERR_INVALID_ARG;
+        }
+        es[v] = make_enc_sym((uint32_t)t.cdf[v], (uint32_t)f);
+      }
     }
-  }
-  std::vector<uint32_t> buf((size_t)ops + 2);
-  BackWriter w{buf.data() + buf.size(), kRansL};
-  // pass 2: encode in reverse symbol order; inside one symbol the pushes were
-  //   [table symbol][count digits...][nibbles low-first], so reversed: nibbles high-first,
-  //   count digits last-first, then the table symbol.
-  for (int64_t i = n - 1; i >= 0; --i) {
-    const int32_t idx = indexes[i];
-    const Table t{cdfs + (int64_t)idx * cdf_stride, cdf_sizes[idx] - 2, offsets[idx]};
     int32_t slot;
     uint32_t raw;
     if (classify(symbols[i], t, slot, raw)) {
       const int nb = nibbles_of(raw);
       for (int j = nb - 1; j >= 0; --j) w.put_bits((raw >> (j * kBypassBits)) & kMaxBypass);
-      const int full = nb / kMaxBypass;  // number of saturated count digits pushed first
+      const int full = nb / kMaxBypass;  // saturated count digits, pushed first by the reference
       w.put_bits((uint32_t)(nb - full * kMaxBypass));
       for (int j = 0; j < full; ++j) w.put_bits((uint32_t)kMaxBypass);
     }
-    const uint32_t start = (uint32_t)t.cdf[slot];
-    const uint32_t freq = (uint32_t)(t.cdf[slot + 1] - t.cdf[slot]);
-    if (freq == 0) {
-      pcc::set_error("pcc_rans_encode_with_indexes: zero-frequency symbol");
-      return PCC_ERR_INVALID_ARG;
-    }
-    w.put(start, freq);
+    w.put(es[slot]);
   }
-  *--w.ptr = (uint32_t)(w.x >> 32);
-  *--w.ptr = (uint32_t)w.x;
-  const int64_t nbytes = (int64_t)((buf.data() + buf.size()) - w.ptr) * 4;
+  w.emit((uint32_t)(w.x >> 32));
+  w.emit((uint32_t)w.x);
+  const int64_t nbytes = (int64_t)(w.buf.size() - w.pos) * 4;
   if (nbytes > out_cap) {
     pcc::set_error("pcc_rans_encode_with_indexes: output capacity %lld < %lld", (long long)out_cap,
                    (long long)nbytes);
     return PCC_ERR_CAPACITY;
   }
-  memcpy(out, w.ptr, (size_t)nbytes);
+  memcpy(out, w.buf.data() + w.pos, (size_t)nbytes);
   return nbytes;
 }
 
@@ -215,6 +259,10 @@ int pcc_rans_decode_with_indexes(const uint8_t* enc, int64_t nbytes, const int32
     refill();
     return v;
   };
+  // per table: slot of the symbol containing cum = bucket << kLutShift, built on first use; the
+  // reference finds the slot with a linear std::find_if over the row, which yields the same slot
+  constexpr int kLutShift = 4;
+  std::vector<std::vector<uint16_t>> lut((size_t)n_tables);
   for (int64_t i = 0; i < n; ++i) {
     const int32_t idx = indexes[i];
     if (idx < 0 || idx >= n_tables) {
@@ -224,10 +272,19 @@ int pcc_rans_decode_with_indexes(const uint8_t* enc, int64_t nbytes, const int32
     const int32_t* cdf = cdfs + (int64_t)idx * cdf_stride;
     const int32_t size = cdf_sizes[idx];
     const int32_t max_value = size - 2;
+    std::vector<uint16_t>& L = lut[idx];
+    if (L.empty()) {
+      L.resize((size_t)(1u << (kPrecision - kLutShift)));
+      int32_t slot = 0;
+      for (uint32_t b = 0; b < L.size(); ++b) {
+        const int32_t c = (int32_t)(b << kLutShift);
+        while (slot + 1 < size - 1 && cdf[slot + 1] <= c) ++slot;
+        L[b] = (uint16_t)slot;
+      }
+    }
     const uint32_t cum = (uint32_t)(x & ((1u << kPrecision) - 1));
-    // first entry > cum (the reference scans linearly with std::find_if; rows are non-decreasing)
-    const int32_t* it = std::upper_bound(cdf, cdf + size, (int32_t)cum);
-    const int32_t s = (int32_t)(it - cdf) - 1;
+    int32_t s = L[cum >> kLutShift];
+    while (cdf[s + 1] <= (int32_t)cum) ++s;  // first entry > cum, minus one
     const uint32_t start = (uint32_t)cdf[s], freq = (uint32_t)(cdf[s + 1] - cdf[s]);
     x = (uint64_t)freq * (x >> kPrecision) + cum - start;
     refill();

@@ -86,6 +86,13 @@ __device__ __forceinline__ int hash_find(const uint64_t* __restrict__ tkeys,
   }
 }
 
+// round an fp32 value to the nearest tf32 (10-bit mantissa), ties away from zero
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+  return __uint_as_float(u);
+}
+
 // ---------------------------------------------------------------- device-wide exclusive scan
 // Three-phase int32 exclusive scan (per-block reduce, single-block scan of the block sums,
 // per-block down-sweep).  ws holds ceil(n / SCAN_TILE) + 1 int32; the grand total is written to

@@ -275,24 +275,34 @@ def tf32_eligible(cin, cout):
 _wt_cache = {}
 
 
-def transposed_weight(w):
-    """[K, cin, cout] -> cached [K, cout, cin] copy for the tensor-core path (pcc_weight_transpose),
-    rebuilt when the parameter is modified in place or re-allocated."""
-    key = w.data_ptr()
-    ver = (w._version, tuple(w.shape), str(w.device))
+def transposed_weight(weight):
+    """[K, cin, cout] -> cached [K, cout, cin] copy for the tensor-core path (pcc_weight_transpose).
+    The cache is keyed on the tensor OBJECT (weak reference) and its in-place version counter, so a
+    modified or re-created parameter is re-laid-out and a recycled address can never alias."""
+    import weakref
+    key = id(weight)
+    ver = (weight._version, tuple(weight.shape), str(weight.device), weight.data_ptr())
     hit = _wt_cache.get(key)
-    if hit is not None and hit[0] == ver:
-        return hit[1]
+    if hit is not None and hit[0]() is weight and hit[1] == ver:
+        return hit[2]
+    if len(_wt_cache) > 512:
+        for k in [k for k, v in _wt_cache.items() if v[0]() is None]:
+            del _wt_cache[k]
+    w = weight.detach()
+    w = (w if w.dim() == 3 else w.unsqueeze(0)).contiguous()
     K, cin, cout = w.shape
     wt = torch.empty((K, cout, cin), dtype=torch.float32, device=w.device)
     check(_L().pcc_weight_transpose(_ptr(w), K, cin, cout, _ptr(wt), _stream()), "pcc_weight_transpose")
     _count()
-    _wt_cache[key] = (ver, wt)
+    _wt_cache[key] = (weakref.ref(weight), ver, wt)
     return wt
 
 
+CONV_ROUND_OUT_TF32 = 1
+
+
 def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None, residual=None,
-         res_rows=None, out=None, mode=None):
+         res_rows=None, out=None, mode=None, round_out=None):
     """out[o] = epilogue(sum_k feats[nbr[k,o]] @ weight[k]).
 
     weight: [K, cin, cout] (or [cin, cout] for K == 1), bias: [1, cout] or [cout].
@@ -310,6 +320,8 @@ def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None
         out = torch.empty((n_out, cout), dtype=torch.float32, device=feats.device)
     if mode is None:
         mode = _default_mode
+    if round_out is None:  # in tf32 mode every activation that can feed a tensor-core layer is stored tf32-rounded
+        round_out = (mode == MODE_TF32 and cout % 32 == 0)
     if mode == MODE_TF32 and not tf32_eligible(cin, cout):
         mode = MODE_EXACT  # stated policy: small-channel layers always run the exact CUDA-core path
     a = ConvArgs()
@@ -317,7 +329,7 @@ def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None
     a.n_in = feats.shape[0]
     a.cin, a.cout = cin, cout
     a.weight = w.data_ptr()
-    wt = transposed_weight(w.detach()) if mode == MODE_TF32 else None
+    wt = transposed_weight(weight) if mode == MODE_TF32 else None
     a.weight_t = None if wt is None else wt.data_ptr()
     b = None if bias is None else bias.contiguous()
     a.bias = None if b is None else b.data_ptr()
@@ -346,6 +358,7 @@ def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None
     a.n_out = n_out
     a.out_stride = out.stride(0) if n_out else cout
     a.mode = mode
+    a.flags = CONV_ROUND_OUT_TF32 if round_out else 0
     if _profile is not None and n_out:
         rec = {"cin": cin, "cout": cout, "K": K, "n_in": int(feats.shape[0]), "n_out": int(n_out),
                "pairs": _pairs(kmap), "mode": int(mode), "ev0": torch.cuda.Event(enable_timing=True),

@@ -137,7 +137,7 @@ class GaussianConditionalOracle:
     def update(self):
         t = self.scale_table.astype(np.float64)
         multiplier = -norm.ppf(self.tail_mass / 2)
-        pmf_center = np.ceil(t * multiplier).astype(np.int32)
+        pmf_center = np.ceil(self.scale_table * np.float32(multiplier)).astype(np.int32)  # float32 product, as torch
         pmf_length = 2 * pmf_center + 1
         max_length = int(pmf_length.max())
         samples = np.abs(np.arange(max_length)[None, :] - pmf_center[:, None]).astype(np.float64)
