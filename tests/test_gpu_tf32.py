@@ -62,7 +62,13 @@ def test_tf32_small_channels_take_exact_path(pcc):
     x = torch.randn((m.n, 4), device=DEV)
     W = torch.randn((27, 4, 64), device=DEV)
     km = m.kernel_map(m, 3)
-    assert torch.equal(ops.conv(x, km, W, None, mode=ops.MODE_TF32), ops.conv(x, km, W, None, mode=ops.MODE_EXACT))
+    ref = ops.conv(x, km, W, None, mode=ops.MODE_EXACT)
+    assert torch.equal(ops.conv(x, km, W, None, mode=ops.MODE_TF32, round_out=False), ref)
+    # by default tf32 mode stores activations rounded to tf32 (round-to-nearest, unbiased), so that
+    # the tensor core's operand truncation downstream is a no-op
+    got = ops.conv(x, km, W, None, mode=ops.MODE_TF32)
+    assert (got - ref).abs().max().item() <= 2.0 ** -11 * ref.abs().max().item() * 1.001
+    assert torch.equal(got.view(torch.int32) & 0x1FFF, torch.zeros_like(got, dtype=torch.int32))
 
 
 def _codec(pcc, mode, radius=26.0, seed=0):
