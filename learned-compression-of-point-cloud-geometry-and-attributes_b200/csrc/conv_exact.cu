@@ -6,7 +6,7 @@
 // Gathered input rows and the weight slice are staged into shared memory with cp.async
 // (zero-fill for missing neighbours), 3 stages deep; each thread keeps an 8 x (TN/16) register
 // tile and issues fp32 FFMA in ascending (k, ci) order, which is the oracle's summation order,
-// so the result is bit-identical to oracle/pcc_oracle.cpp::orc_conv.  No atomics.
+// so the result is bit-identical to the CPU oracle's sparse-conv restatement.  No atomics.
 //
 // Roofline: FP32 FMA pipe for cin, cout >= 32 (148 SMs x 128 lanes x 2 flop x clock); the
 // gathers are served by L2 because rows are in lexicographic order.
