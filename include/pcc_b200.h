@@ -88,15 +88,23 @@ int pcc_coords_expand(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, 
                       int64_t n, int kernel_size, int32_t ts_in, uint64_t* out_keys, int64_t* n_out,
                       void* ws, size_t ws_bytes, void* stream);
 
-/* Kernel map (ME kernel_map.cuh) of every convolution on the path.  For output key o and kernel
- * offset k (ME order: first spatial axis fastest; size 3 -> {-1,0,1}^3, size 2 -> {0,1}^3):
- *     nbr[k * nbr_stride + o] = row of (c_o + d_k * step) in the hashed input map, or -1
+/* Kernel map (ME kernel_map.cuh) of every convolution on the path.  For tile row j (output row
+ * o = order ? order[j] : j) and kernel offset k (ME order: first spatial axis fastest; size 3 ->
+ * {-1,0,1}^3, size 2 -> {0,1}^3):
+ *     nbr[k * nbr_stride + j] = row of (c_o + d_k * step) in the hashed input map, or -1
  * step = +input tensor stride for (strided) convolution, -output tensor stride for transposed
  * convolution.  in_align = input tensor stride: targets not aligned to it are not probed.
- * tapmask[o / PCC_TILE_M] bit k is set iff some row of that tile has a neighbour at offset k. */
+ * tapmask[j / PCC_TILE_M] bit k is set iff some row of that tile has a neighbour at offset k.
+ * order [dev, n_out] (may be NULL = identity) RECEIVES the tile-row permutation: output rows
+ * sorted by (row / seg_rows, neighbour mask), so that rows with the same neighbour pattern share
+ * a tile and the convolution skips the offsets a tile does not have (the reference's ME kernel
+ * map keeps per-offset pair lists for the same purpose).  seg_rows: power of two >= PCC_TILE_M.
+ * ws: pcc_kernel_map_ws_bytes(n_out) bytes of scratch, needed only with order. */
+size_t pcc_kernel_map_ws_bytes(int64_t n_out);
 int pcc_kernel_map(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, const uint64_t* out_keys,
                    int64_t n_out, int kernel_size, int32_t step, int32_t in_align, int32_t* nbr,
-                   int64_t nbr_stride, uint32_t* tapmask, void* stream);
+                   int64_t nbr_stride, uint32_t* tapmask, int32_t* order, int64_t seg_rows, void* ws,
+                   size_t ws_bytes, void* stream);
 
 /* ------------------------------------------------------------------ sparse convolution
  * Replaces ME convolution_kernel.cu / convolution_transpose_gpu.cu behind ME.MinkowskiConvolution
@@ -107,7 +115,8 @@ int pcc_kernel_map(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, con
  *   activation                               (ME.MinkowskiReLU / MinkowskiLeakyReLU, 32 sites)
  *   * beta + gamma                           (ScaledBlock FiLM, model/blocks.py:37-40)
  *   + residual                               (ScaledBlock skip, model/blocks.py:49-52)
- * Output-stationary: out[o] = sum_k in[nbr[k][o]] @ W[k]; no atomics, fixed summation order. */
+ * Output-stationary: out[order[j]] = sum_k in[nbr[k][j]] @ W[k]; no atomics, fixed summation order.
+ * film_rows / res_rows are indexed by OUTPUT row. */
 #define PCC_ACT_NONE 0
 #define PCC_ACT_RELU 1
 #define PCC_ACT_LEAKY 2
@@ -144,6 +153,7 @@ typedef struct pcc_conv_args {
   int32_t mode;             /* PCC_MODE_* */
   int32_t flags;            /* PCC_CONV_* bit set */
   const float* weight_t;    /* [dev, K x cout x cin] (pcc_weight_transpose); required by PCC_MODE_TF32 */
+  const int32_t* order;     /* [dev, n_out] tile row -> output row (pcc_kernel_map), NULL = identity */
 } pcc_conv_args;
 
 int pcc_conv_fwd(const pcc_conv_args* args, void* stream);

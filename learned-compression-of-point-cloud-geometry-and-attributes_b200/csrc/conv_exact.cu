@@ -40,6 +40,7 @@ struct ConvParams {
   const int32_t* film_rows;
   const float* residual;
   const int32_t* res_rows;
+  const int32_t* order;
   float* out;
   int64_t nbr_stride, n_out, out_stride;
   int cin, cout, K, act, film_c, flags;
@@ -75,10 +76,25 @@ conv_exact_kernel(const ConvParams p) {
 #pragma unroll
     for (int c = 0; c < CN; ++c) acc[i][c] = 0.0f;
 
-  // producer cursor
+  // producer cursor.  The kernel-map rows of the current offset (idx) and of the next active
+  // offset (nidx) are held in registers: the next offset's indices are requested when the current
+  // one starts, so the gather addresses never wait on a dependent load.
   uint32_t pmask = mask;
   int pk = pmask ? (__ffs(pmask) - 1) : 0;
   int pchunk = 0;
+  int idx[4], nidx[4];
+  auto load_idx = [&](int k, int (&dst)[4]) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t t = tile_base + (tid >> 3) + 32 * j;
+      dst[j] = (t < p.n_out) ? __ldg(p.nbr + (int64_t)k * p.nbr_stride + t) : -1;
+    }
+  };
+  {
+    load_idx(pk, idx);
+    const uint32_t rest = pmask & (pmask - 1);
+    if (rest) load_idx(__ffs(rest) - 1, nidx);
+  }
 
   auto issue = [&](int stage) {
     const int ci0 = pchunk * CE_TK;
@@ -89,20 +105,18 @@ conv_exact_kernel(const ConvParams p) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int r = (tid >> 3) + 32 * j;
-        const int64_t o = tile_base + r;
-        int idx = -1;
-        if (o < p.n_out) idx = __ldg(p.nbr + (int64_t)pk * p.nbr_stride + o);
+        const int ix = idx[j];
         float* dst = &sm.a[stage][r][q * 4];
         if (VEC) {
-          const bool ok = idx >= 0 && ci < p.cin;
-          const float* src = ok ? p.in + (int64_t)idx * p.cin + ci : p.in;
+          const bool ok = ix >= 0 && ci < p.cin;
+          const float* src = ok ? p.in + (int64_t)ix * p.cin + ci : p.in;
           cp_async16(dst, src, ok ? 16 : 0);
         } else {
           float v[4] = {0.f, 0.f, 0.f, 0.f};
-          if (idx >= 0) {
+          if (ix >= 0) {
 #pragma unroll
             for (int e = 0; e < 4; ++e)
-              if (ci + e < p.cin) v[e] = __ldg(p.in + (int64_t)idx * p.cin + ci + e);
+              if (ci + e < p.cin) v[e] = __ldg(p.in + (int64_t)ix * p.cin + ci + e);
           }
           *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
         }
@@ -138,6 +152,10 @@ conv_exact_kernel(const ConvParams p) {
       pchunk = 0;
       pmask &= pmask - 1;
       pk = pmask ? (__ffs(pmask) - 1) : 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) idx[j] = nidx[j];
+      const uint32_t rest = pmask & (pmask - 1);
+      if (rest) load_idx(__ffs(rest) - 1, nidx);
     }
   };
 
@@ -193,8 +211,9 @@ conv_exact_kernel(const ConvParams p) {
   // ---- epilogue: bias -> activation -> FiLM -> residual -> store
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    const int64_t o = tile_base + ty + 16 * i;
-    if (o >= p.n_out) continue;
+    const int64_t t = tile_base + ty + 16 * i;  // tile row -> output row
+    if (t >= p.n_out) continue;
+    const int64_t o = p.order ? (int64_t)__ldg(p.order + t) : t;
     int64_t frow = o, rrow = o;
     if (p.film_c && p.film_rows) frow = __ldg(p.film_rows + o);
     if (p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
@@ -251,7 +270,7 @@ int conv_exact(const pcc_conv_args* a, cudaStream_t st) {
   ConvParams p;
   p.in = a->in; p.weight = a->weight; p.bias = a->bias; p.nbr = a->nbr; p.tapmask = a->tapmask;
   p.film = a->film; p.film_rows = a->film_rows; p.residual = a->residual; p.res_rows = a->res_rows;
-  p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
+  p.order = a->order; p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
   p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope; p.flags = a->flags;
   if (a->cout > 64) return launch_exact<128>(p, st);
   if (a->cout > 32) return launch_exact<64>(p, st);

@@ -26,10 +26,12 @@ namespace pcc {
 
 constexpr int TC_TM = PCC_TILE_M;      // 128 rows = UMMA M
 constexpr int TC_TK = 32;              // fp32 channels per stage = 128 bytes = one swizzle row
-constexpr int TC_STAGES = 4;          // = TC_LAG + 2: one stage being consumed, one published, two landing
+constexpr int TC_STAGES = 3;          // = TC_LAG + 2: one stage being consumed, one published, one landing
 constexpr int TC_PRODUCERS = 128;      // warps 0-3
 constexpr int TC_THREADS = 160;        // + warp 4 (MMA issuer, TMEM allocator)
-constexpr int TC_LAG = 2;              // cp.async groups a producer thread keeps in flight
+constexpr int TC_LAG = 1;              // cp.async groups a producer thread keeps in flight
+// Two CTAs are resident per SM (3 x 32 KB stages + the tile's kernel-map rows each): one CTA's
+// epilogue and pipeline fill overlap the other's MMA stream.
 
 struct TcParams {
   const float* in;
@@ -41,6 +43,7 @@ struct TcParams {
   const int32_t* film_rows;
   const float* residual;
   const int32_t* res_rows;
+  const int32_t* order;
   float* out;
   int64_t nbr_stride, n_out, out_stride;
   int cin, cout, K, act, film_c, flags;
@@ -142,11 +145,12 @@ struct TcSmem {
   static constexpr int B_BYTES = BN * 128;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int BAR_OFFSET = TC_STAGES * STAGE_BYTES;
-  static constexpr int TOTAL = BAR_OFFSET + 128 + 1024;  // + barriers/tmem slot + alignment slack
+  static constexpr int NBR_OFFSET = BAR_OFFSET + 128;      // int32 [active taps <= 27][128 rows]
+  static constexpr int TOTAL = NBR_OFFSET + 27 * TC_TM * 4 + 1024;  // + alignment slack
 };
 
 template <int BN>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(TC_THREADS, 2)
 conv_tf32_kernel(const TcParams p) {
   extern __shared__ unsigned char smem_raw[];
   // 1024-byte alignment for the swizzle atoms
@@ -180,6 +184,20 @@ conv_tf32_kernel(const TcParams p) {
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   if (warp == 4) tmem_alloc(tmem_slot, TMEM_COLS);
+  // the tile's kernel-map rows for its active offsets, staged once (coalesced) so that gather
+  // addresses never wait on a dependent global load
+  int32_t* s_nbr = reinterpret_cast<int32_t*>(sbase + S::NBR_OFFSET);
+  {
+    const int nact = __popc(mask);
+    for (int a = warp; a < nact; a += TC_THREADS / 32) {
+      const int k = __fns(mask, 0, a + 1);
+#pragma unroll
+      for (int r = lane; r < TC_TM; r += 32) {
+        const int64_t t = tile_base + r;
+        s_nbr[a * TC_TM + r] = (t < p.n_out) ? __ldg(p.nbr + (int64_t)k * p.nbr_stride + t) : -1;
+      }
+    }
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -191,6 +209,7 @@ conv_tf32_kernel(const TcParams p) {
     const int rbase = tid >> 3;  // rows rbase + 16 j
     uint32_t pmask = mask;
     int pk = pmask ? (__ffs(pmask) - 1) : 0;
+    int pa = 0;  // ordinal of pk among the active offsets
     int pchunk = 0;
     int idx[8];
     bool need_idx = true;
@@ -199,10 +218,7 @@ conv_tf32_kernel(const TcParams p) {
       if (s >= TC_STAGES) mbar_wait(empty_bar(stage), (uint32_t)(((s / TC_STAGES) - 1) & 1));
       if (need_idx) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int64_t o = tile_base + rbase + 16 * j;
-          idx[j] = (o < p.n_out) ? __ldg(p.nbr + (int64_t)pk * p.nbr_stride + o) : -1;
-        }
+        for (int j = 0; j < 8; ++j) idx[j] = s_nbr[pa * TC_TM + rbase + 16 * j];
         need_idx = false;
       }
       const uint32_t a_stage = base + stage * S::STAGE_BYTES;
@@ -233,6 +249,7 @@ conv_tf32_kernel(const TcParams p) {
         pchunk = 0;
         pmask &= pmask - 1;
         pk = pmask ? (__ffs(pmask) - 1) : 0;
+        ++pa;
         need_idx = true;
       }
     }
@@ -269,8 +286,9 @@ conv_tf32_kernel(const TcParams p) {
       mbar_wait(accum_bar, 0);
       tc_fence_after();
     }
-    const int64_t o = tile_base + warp * 32 + lane;
-    const bool live = o < p.n_out;
+    const int64_t t = tile_base + warp * 32 + lane;  // tile row -> output row
+    const bool live = t < p.n_out;
+    const int64_t o = (live && p.order) ? (int64_t)__ldg(p.order + t) : t;
     int64_t frow = o, rrow = o;
     if (live && p.film_c && p.film_rows) frow = __ldg(p.film_rows + o);
     if (live && p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
@@ -348,7 +366,7 @@ int conv_tf32(const pcc_conv_args* a, cudaStream_t st) {
   TcParams p;
   p.in = a->in; p.weight_t = a->weight_t; p.bias = a->bias; p.nbr = a->nbr; p.tapmask = a->tapmask;
   p.film = a->film; p.film_rows = a->film_rows; p.residual = a->residual; p.res_rows = a->res_rows;
-  p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
+  p.order = a->order; p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
   p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope; p.flags = a->flags;
   if (a->cout % 128 == 0 || a->cout > 128) return launch_tc<128>(p, st);
   if (a->cout > 64) return launch_tc<128>(p, st);

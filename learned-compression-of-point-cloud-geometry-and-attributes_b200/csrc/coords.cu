@@ -204,24 +204,39 @@ __global__ void expand_emit_kernel(const uint64_t* __restrict__ keys, int64_t n,
 }
 
 // ---------------------------------------------------------------- kernel map
-// One thread per output row, looping over the K offsets: key reads and nbr writes are coalesced
-// across the warp (nbr is offset-major), the warp votes the per-tile tap mask, and the K
-// independent probes per thread give the memory system K-deep parallelism.
-template <int KS>
+// One thread per tile row, looping over the K offsets: nbr writes are coalesced across the warp
+// (nbr is offset-major), the warp votes the per-tile tap mask, and the K independent probes per
+// thread give the memory system K-deep parallelism.
+//
+// Tile rows.  The convolution kernels skip, per 128-row tile, every kernel offset no row of the
+// tile has a neighbour at.  In lexicographic row order a tile of a voxelised surface has nearly all
+// 27 offsets active although a row has only 10-14 neighbours (and a generative transposed
+// convolution has 1-8 of 27 by parity class), so most of the tile's multiply-adds would be spent on
+// zero rows.  With `order` the tile rows are a permutation of the output rows: rows sorted by
+// (row / seg_rows, 27-bit neighbour mask), i.e. rows with the same neighbour pattern share tiles
+// while a tile's gathers stay inside one L2-sized segment of the map.  Pass 1 (MASK_ONLY) computes
+// the sort keys, a radix sort yields `order`, pass 2 writes nbr / tapmask in tile-row order.
+template <int KS, bool MASK_ONLY>
 __global__ void __launch_bounds__(PCC_TILE_M)
 kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict__ tvals,
                   uint64_t cap_mask, const uint64_t* __restrict__ out_keys, int64_t n_out, int step,
-                  int in_align, int32_t* __restrict__ nbr, int64_t nbr_stride,
-                  uint32_t* __restrict__ tapmask) {
+                  int in_align, const int32_t* __restrict__ order, int32_t* __restrict__ nbr,
+                  int64_t nbr_stride, uint32_t* __restrict__ tapmask, uint64_t* __restrict__ sort_keys,
+                  int seg_shift) {
   constexpr int K = KS * KS * KS;
   constexpr int LO = (KS == 3) ? -1 : 0;
   __shared__ uint32_t smask;
-  if (threadIdx.x == 0) smask = 0;
-  __syncthreads();
-  const int64_t o = (int64_t)blockIdx.x * PCC_TILE_M + threadIdx.x;
-  const bool live = o < n_out;
+  if (!MASK_ONLY) {
+    if (threadIdx.x == 0) smask = 0;
+    __syncthreads();
+  }
+  const int64_t j = (int64_t)blockIdx.x * PCC_TILE_M + threadIdx.x;  // tile row
+  const bool live = j < n_out;
   int b = 0, x = 0, y = 0, z = 0;
-  if (live) unpack_key(out_keys[o], b, x, y, z);
+  if (live) {
+    const int64_t o = (!MASK_ONLY && order) ? (int64_t)__ldg(order + j) : j;
+    unpack_key(out_keys[o], b, x, y, z);
+  }
   uint32_t mine = 0;
   const int amask = in_align - 1;  // in_align is a power of two
 #pragma unroll 3
@@ -232,8 +247,12 @@ kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict_
     if (live && coord_in_range(qx) && coord_in_range(qy) && coord_in_range(qz) &&
         (((qx | qy | qz) & amask) == 0))
       r = hash_find(tkeys, tvals, cap_mask, pack_key(b, qx, qy, qz));
-    if (live) nbr[(int64_t)k * nbr_stride + o] = r;
+    if (!MASK_ONLY && live) nbr[(int64_t)k * nbr_stride + j] = r;
     if (r >= 0) mine |= 1u << k;
+  }
+  if (MASK_ONLY) {
+    if (live) sort_keys[j] = ((uint64_t)(j >> seg_shift) << 27) | mine;
+    return;
   }
 #pragma unroll
   for (int s = 16; s > 0; s >>= 1) mine |= __shfl_xor_sync(0xffffffffu, mine, s);
@@ -453,31 +472,74 @@ int pcc_coords_expand(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, 
   return PCC_OK;
 }
 
+size_t pcc_kernel_map_ws_bytes(int64_t n_out) {
+  if (n_out <= 0) return 256;
+  // sort keys in | sort keys out | iota | cub
+  return align_up((size_t)n_out * 8, 256) * 2 + align_up((size_t)n_out * 4, 256) +
+         align_up(cub_sort_pairs_bytes(n_out), 256);
+}
+
+}  // extern "C"
+
+template <int KS>
+static int kernel_map_launch(const uint64_t* tkeys, const int32_t* tvals, uint64_t cm, const uint64_t* out_keys,
+                             int64_t n_out, int32_t step, int32_t in_align, int32_t* nbr, int64_t nbr_stride,
+                             uint32_t* tapmask, int32_t* order, int64_t seg_rows, void* ws, size_t ws_bytes,
+                             cudaStream_t st) {
+  const unsigned grid = (unsigned)ceil_div(n_out, PCC_TILE_M);
+  if (order) {
+    int seg_shift = 0;
+    while (((int64_t)1 << seg_shift) < seg_rows) ++seg_shift;
+    int seg_bits = 0;
+    while ((((n_out - 1) >> seg_shift) >> seg_bits) > 0) ++seg_bits;
+    char* w = reinterpret_cast<char*>(ws);
+    uint64_t* k_in = reinterpret_cast<uint64_t*>(w);
+    uint64_t* k_out = reinterpret_cast<uint64_t*>(w + align_up((size_t)n_out * 8, 256));
+    int32_t* iota = reinterpret_cast<int32_t*>(w + 2 * align_up((size_t)n_out * 8, 256));
+    void* cub_ws = w + 2 * align_up((size_t)n_out * 8, 256) + align_up((size_t)n_out * 4, 256);
+    size_t cub_bytes = align_up(cub_sort_pairs_bytes(n_out), 256);
+    kernel_map_kernel<KS, true><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align,
+                                                            nullptr, nullptr, 0, nullptr, k_in, seg_shift);
+    PCC_CHECK_LAUNCH("kernel_map_kernel<mask>");
+    iota_kernel<<<grid_for(n_out), THREADS, 0, st>>>(iota, n_out);
+    PCC_CHECK_LAUNCH("iota_kernel");
+    PCC_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(cub_ws, cub_bytes, k_in, k_out, iota, order, (int)n_out, 0,
+                                                   27 + seg_bits, st));
+  }
+  kernel_map_kernel<KS, false><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align,
+                                                           order, nbr, nbr_stride, tapmask, nullptr, 0);
+  PCC_CHECK_LAUNCH("kernel_map_kernel");
+  return PCC_OK;
+}
+
+extern "C" {
+
 int pcc_kernel_map(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, const uint64_t* out_keys,
                    int64_t n_out, int kernel_size, int32_t step, int32_t in_align, int32_t* nbr,
-                   int64_t nbr_stride, uint32_t* tapmask, void* stream) {
+                   int64_t nbr_stride, uint32_t* tapmask, int32_t* order, int64_t seg_rows, void* ws,
+                   size_t ws_bytes, void* stream) {
   if (n_out == 0) return PCC_OK;
   PCC_REQUIRE(tkeys && tvals && out_keys && nbr, "null pointer");
+  PCC_REQUIRE(n_out < (1ll << 31), "n_out out of range");
   PCC_REQUIRE(nbr_stride >= n_out, "nbr_stride < n_out");
   PCC_REQUIRE(in_align > 0 && (in_align & (in_align - 1)) == 0, "in_align must be a power of two");
   PCC_REQUIRE((cap & (cap - 1)) == 0, "capacity must be a power of two");
+  if (order) {
+    PCC_REQUIRE(seg_rows >= PCC_TILE_M && (seg_rows & (seg_rows - 1)) == 0, "seg_rows must be a power of two >= 128");
+    PCC_REQUIRE(ws && ws_bytes >= pcc_kernel_map_ws_bytes(n_out), "workspace too small");
+  }
   cudaStream_t st = (cudaStream_t)stream;
-  const unsigned grid = (unsigned)ceil_div(n_out, PCC_TILE_M);
   const uint64_t cm = (uint64_t)cap - 1;
   switch (kernel_size) {
     case 1:
-      kernel_map_kernel<1><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask);
-      break;
+      return kernel_map_launch<1>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask, order, seg_rows, ws, ws_bytes, st);
     case 2:
-      kernel_map_kernel<2><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask);
-      break;
+      return kernel_map_launch<2>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask, order, seg_rows, ws, ws_bytes, st);
     case 3:
-      kernel_map_kernel<3><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask);
-      break;
+      return kernel_map_launch<3>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask, order, seg_rows, ws, ws_bytes, st);
     default:
       PCC_REQUIRE(false, "kernel_size must be 1, 2 or 3");
   }
-  PCC_CHECK_LAUNCH("kernel_map_kernel");
   return PCC_OK;
 }
 

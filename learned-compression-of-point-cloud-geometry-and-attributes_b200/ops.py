@@ -86,11 +86,22 @@ def sort_keys(keys, want_perm=True):
 
 
 class KernelMap:
-    """nbr [K, stride] int32 (offset-major), tapmask [ceil(n_out/128)] uint32 (as int32)."""
-    __slots__ = ("nbr", "tapmask", "K", "n_out", "stride", "_pairs_cache")
+    """nbr [K, stride] int32 (offset-major, indexed by TILE ROW), tapmask [ceil(n_out/128)] uint32
+    (as int32), order [n_out] int32: tile row -> output row (None = identity)."""
+    __slots__ = ("nbr", "tapmask", "K", "n_out", "stride", "order", "_pairs_cache")
 
-    def __init__(self, nbr, tapmask, K, n_out, stride):
+    def __init__(self, nbr, tapmask, K, n_out, stride, order=None):
         self.nbr, self.tapmask, self.K, self.n_out, self.stride = nbr, tapmask, K, n_out, stride
+        self.order = order
+
+    def natural_nbr(self):
+        """nbr re-indexed by output row ([K, n_out]); what the oracle's kernel map holds."""
+        nbr = self.nbr[:, :self.n_out]
+        if self.order is None:
+            return nbr
+        out = torch.empty_like(nbr)
+        out[:, self.order.long()] = nbr
+        return out
 
 
 class CoordMap:
@@ -191,16 +202,33 @@ class CoordMap:
         stride = max(n_out, 1)
         nbr = torch.empty((K, stride), dtype=torch.int32, device=self.device)
         tapmask = torch.empty(max((n_out + TILE_M - 1) // TILE_M, 1), dtype=torch.int32, device=self.device)
+        order = None
         if n_out:
             tk, tv, cap = self.hash()
             step = -out_map.ts if transpose else self.ts
             align = self.ts if transpose else 1
+            ws, wsb = None, 0
+            if K > 1 and n_out > TILE_M and _tile_seg_rows:
+                order = torch.empty(n_out, dtype=torch.int32, device=self.device)
+                wsb = _L().pcc_kernel_map_ws_bytes(n_out)
+                ws = _ws(wsb, self.device)
             check(_L().pcc_kernel_map(_ptr(tk), _ptr(tv), cap, _ptr(out_map.keys), n_out, kernel_size, step,
-                                      align, _ptr(nbr), stride, _ptr(tapmask), _stream()), "pcc_kernel_map")
-            _count()
-        kmap = KernelMap(nbr, tapmask, K, n_out, stride)
+                                      align, _ptr(nbr), stride, _ptr(tapmask), _ptr(order), _tile_seg_rows,
+                                      _ptr(ws), wsb, _stream()), "pcc_kernel_map")
+            _count(1 if order is None else 7)
+        kmap = KernelMap(nbr, tapmask, K, n_out, stride, order)
         self._kmaps[key] = (out_map, kmap)
         return kmap
+
+
+_tile_seg_rows = 1 << 17  # rows per segment of the tile-row sort (0 = keep lexicographic tiles)
+
+
+def set_tile_segment_rows(n):
+    """Segment length of the kernel map's tile-row sort (power of two >= 128; 0 disables it).
+    Affects only maps built afterwards; results are independent of it."""
+    global _tile_seg_rows
+    _tile_seg_rows = int(n)
 
 
 def make_map(coords_or_keys, ts=1, assume_sorted=False):
@@ -359,6 +387,7 @@ def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None
     a.out_stride = out.stride(0) if n_out else cout
     a.mode = mode
     a.flags = CONV_ROUND_OUT_TF32 if round_out else 0
+    a.order = None if kmap.order is None else kmap.order.data_ptr()
     if _profile is not None and n_out:
         rec = {"cin": cin, "cout": cout, "K": K, "n_in": int(feats.shape[0]), "n_out": int(n_out),
                "pairs": _pairs(kmap), "mode": int(mode), "ev0": torch.cuda.Event(enable_timing=True),

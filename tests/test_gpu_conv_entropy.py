@@ -196,3 +196,38 @@ def test_color_finalize(pcc, oracle):
     ref = np.clip(np.rint(f * np.float32(255)), 0, 255).astype(np.float32) / np.float32(255)
     assert np.array_equal(got[:, 3:], ref)
     assert np.array_equal(got[:, :3], m.coords.cpu().numpy()[:, 1:].astype(np.float32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seg", [0, 128, 1024, 1 << 17])
+def test_conv_independent_of_tile_order(pcc, oracle, seg):
+    """The tile-row permutation of the kernel map (rows grouped by neighbour mask) must not change
+    a single bit of the result, in either mode, with FiLM / residual row lookups in the epilogue."""
+    ops = pcc.ops
+    rng = np.random.default_rng(5)
+    old = ops._tile_seg_rows
+    try:
+        ops.set_tile_segment_rows(seg)
+        m, keys, cs = _setup(pcc, oracle, 6000, 30, 1, 77)
+        n, cin, cout = m.n, 64, 128
+        x = rng.standard_normal((n, cin)).astype(np.float32)
+        W = (rng.standard_normal((27, cin, cout)) / np.sqrt(cin * 9)).astype(np.float32)
+        b = rng.standard_normal((1, cout)).astype(np.float32)
+        film = rng.standard_normal((n // 2, 2 * cout)).astype(np.float32)
+        frows = rng.integers(-1, n // 2, size=n).astype(np.int32)
+        res = rng.standard_normal((n, cout)).astype(np.float32)
+        nbr = oracle.prims.kernel_map(keys, cs, oracle.prims.kernel_offsets(3))
+        ref = oracle.prims.relu(oracle.prims.conv_apply(x, nbr, W, b))
+        g = np.where(frows[:, None] >= 0, film[np.maximum(frows, 0)], np.float32(0))
+        ref = ((ref * g[:, :cout] + g[:, cout:]).astype(np.float32) + res).astype(np.float32)
+        km = m.kernel_map(m, 3)
+        assert (km.order is None) == (seg == 0)
+        t = lambda a: torch.from_numpy(a).to(DEV)
+        got = ops.conv(t(x), km, t(W), t(b), act=1, film=t(film), film_rows=t(frows), residual=t(res),
+                       mode=ops.MODE_EXACT)
+        assert np.array_equal(got.cpu().numpy().view(np.uint32), ref.view(np.uint32))
+        g32 = ops.conv(t(x), km, t(W), t(b), act=1, film=t(film), film_rows=t(frows), residual=t(res),
+                       mode=ops.MODE_TF32, round_out=False)
+        assert (g32 - got).abs().max().item() <= 2e-2
+    finally:
+        ops.set_tile_segment_rows(old)

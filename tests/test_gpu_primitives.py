@@ -100,21 +100,31 @@ def test_kernel_map_conv(pcc, oracle, ks, n, extent, ts):
     # stride 1
     km = m.kernel_map(m, ks)
     ref = oracle.prims.kernel_map(keys, cs, offs)
-    assert np.array_equal(km.nbr[:, :km.n_out].cpu().numpy(), ref)
-    # tap mask
+    assert np.array_equal(km.natural_nbr().cpu().numpy(), ref)
+    # tile rows: `order` is a permutation (sorted by neighbour mask inside lexicographic segments)
+    # and the tap mask is the OR over the rows of each 128-row tile in that order
+    order = np.arange(ref.shape[1]) if km.order is None else km.order.cpu().numpy()
+    assert np.array_equal(np.sort(order), np.arange(ref.shape[1]))
+    tiled = ref[:, order]
+    assert np.array_equal(km.nbr[:, :km.n_out].cpu().numpy(), tiled)
+    if km.order is not None:
+        seg = pcc.ops._tile_seg_rows
+        rowmask = ((ref >= 0).astype(np.int64) << np.arange(ref.shape[0])[:, None]).sum(0)
+        sortkey = ((np.arange(ref.shape[1]) // seg) << 27) | rowmask
+        assert np.array_equal(order, np.argsort(sortkey, kind="stable"))
     tiles = (ref.shape[1] + 127) // 128
     tm = km.tapmask.cpu().numpy().view(np.uint32)
     for t in range(tiles):
         want = 0
         for k in range(ref.shape[0]):
-            if (ref[k, t * 128:(t + 1) * 128] >= 0).any():
+            if (tiled[k, t * 128:(t + 1) * 128] >= 0).any():
                 want |= 1 << k
         assert tm[t] == want
     # stride 2
     s = m.stride2()
     km2 = m.kernel_map(s, ks)
     ref2 = oracle.prims.kernel_map(keys, oracle.prims.stride_coords(c, 2 * ts), offs)
-    assert np.array_equal(km2.nbr[:, :km2.n_out].cpu().numpy(), ref2)
+    assert np.array_equal(km2.natural_nbr().cpu().numpy(), ref2)
 
 
 @pytest.mark.parametrize("ks", [2, 3])
@@ -128,7 +138,7 @@ def test_kernel_map_transpose(pcc, oracle, ks, n, extent, ts):
     km = m.kernel_map(e, ks, transpose=True)
     ref = oracle.prims.kernel_map(keys, oracle.prims.expand_coords(c, ks, ts // 2),
                                   -oracle.prims.kernel_offsets(ks) * (ts // 2))
-    got = km.nbr[:, :km.n_out].cpu().numpy()
+    got = km.natural_nbr().cpu().numpy()
     assert np.array_equal(got, ref)
     assert (got >= 0).sum() == ks ** 3 * m.n  # generative: pairs = K * N_in exactly (Appendix A5)
 
