@@ -10,6 +10,8 @@
 //
 // Roofline: FP32 FMA pipe for cin, cout >= 32 (148 SMs x 128 lanes x 2 flop x clock); the
 // gathers are served by L2 because rows are in lexicographic order.
+#include <stdlib.h>
+
 #include "pcc_common.cuh"
 
 namespace pcc {
@@ -54,15 +56,40 @@ struct ExactSmem {
 };
 
 // VEC: cin % 4 == 0 && cout % 4 == 0 (16-byte cp.async sources are aligned)
-template <int TN, bool VEC>
+// F2: accumulate with the packed fma.rn.f32x2 (two independent IEEE fp32 FMAs per lane and
+// instruction — the same roundings as two scalar FMAs, half the issue slots)
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(unsigned long long v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ void ffma2(unsigned long long& d, unsigned long long a, unsigned long long b) {
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
+}
+
+template <int TN, bool VEC, bool F2>
 __global__ void __launch_bounds__(CE_THREADS, 2)
 conv_exact_kernel(const ConvParams p) {
   constexpr int CN = TN / 16;  // output channels per thread
+  constexpr int AV = 4;        // floats of a gathered row per shared-memory load (LDS.128)
+  constexpr bool PK = F2 && (CN % 2 == 0);
+  constexpr int CP = PK ? CN / 2 : 1;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   ExactSmem<TN>& sm = *reinterpret_cast<ExactSmem<TN>*>(smem_raw);
 
   const int tid = threadIdx.x;
-  const int tx = tid & 15, ty = tid >> 4;
+  // compute mapping: warp w owns rows 32 (w >> 1) .. +31 and columns (TN / 2)(w & 1) .. ; inside the
+  // warp, lane = ty * 8 + tx: thread rows rbase + 4 i, thread columns cbase (+ 32 for the second
+  // quad when CN == 8).  For one k-slice the four ty of a warp read 4 rows x 16 B (one conflict-free
+  // shared-memory wavefront, broadcast over tx) and the eight tx read 128 contiguous bytes of the
+  // weight row (one wavefront, broadcast over ty).
+  const int lane = tid & 31, wid = tid >> 5;
+  const int tx = lane & 7, ty = lane >> 3;
+  const int rbase = (wid >> 1) * 32 + ty;
+  const int cbase = (wid & 1) * (TN / 2) + tx * (CN == 8 ? 4 : CN);
   const int64_t tile_base = (int64_t)blockIdx.x * CE_TM;
   const int co_base = blockIdx.y * TN;
   const int nchunks = (p.cin + CE_TK - 1) / CE_TK;
@@ -71,10 +98,14 @@ conv_exact_kernel(const ConvParams p) {
   const int nsteps = __popc(mask) * nchunks;
 
   float acc[8][CN];
+  unsigned long long acc2[8][CP];
 #pragma unroll
-  for (int i = 0; i < 8; ++i)
+  for (int i = 0; i < 8; ++i) {
 #pragma unroll
     for (int c = 0; c < CN; ++c) acc[i][c] = 0.0f;
+#pragma unroll
+    for (int c = 0; c < CP; ++c) acc2[i][c] = 0ull;
+  }
 
   // producer cursor.  The kernel-map rows of the current offset (idx) and of the next active
   // offset (nidx) are held in registers: the next offset's indices are requested when the current
@@ -174,44 +205,69 @@ conv_exact_kernel(const ConvParams p) {
 
     const int st = s % CE_STAGES;
 #pragma unroll
-    for (int k4 = 0; k4 < CE_TK / 4; ++k4) {
-      float4 a4[8];
+    for (int kv = 0; kv < CE_TK / AV; ++kv) {
+      float a[8][AV];
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
-        a4[i] = *reinterpret_cast<const float4*>(&sm.a[st][ty + 16 * i][k4 * 4]);
+      for (int i = 0; i < 8; ++i) {
+        const float* ap = &sm.a[st][rbase + 4 * i][kv * AV];
+        if (AV == 4) {
+          const float4 v = *reinterpret_cast<const float4*>(ap);
+          a[i][0] = v.x; a[i][1] = v.y; a[i][2 % AV] = v.z; a[i][3 % AV] = v.w;
+        } else {
+          const float2 v = *reinterpret_cast<const float2*>(ap);
+          a[i][0] = v.x; a[i][1] = v.y;
+        }
+      }
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
+      for (int e = 0; e < AV; ++e) {
         float b[CN];
-        const float* brow = &sm.b[st][k4 * 4 + e][0];
+        const float* brow = &sm.b[st][kv * AV + e][0];
         if (CN == 8) {
-          const float4 b0 = *reinterpret_cast<const float4*>(brow + tx * 4);
-          const float4 b1 = *reinterpret_cast<const float4*>(brow + 64 + tx * 4);
+          const float4 b0 = *reinterpret_cast<const float4*>(brow + cbase);
+          const float4 b1 = *reinterpret_cast<const float4*>(brow + cbase + 32);
           b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w;
           b[4 % CN] = b1.x; b[5 % CN] = b1.y; b[6 % CN] = b1.z; b[7 % CN] = b1.w;
         } else if (CN == 4) {
-          const float4 b0 = *reinterpret_cast<const float4*>(brow + tx * 4);
+          const float4 b0 = *reinterpret_cast<const float4*>(brow + cbase);
           b[0] = b0.x; b[1 % CN] = b0.y; b[2 % CN] = b0.z; b[3 % CN] = b0.w;
         } else if (CN == 2) {
-          const float2 b0 = *reinterpret_cast<const float2*>(brow + tx * 2);
+          const float2 b0 = *reinterpret_cast<const float2*>(brow + cbase);
           b[0] = b0.x; b[1 % CN] = b0.y;
         } else {
-          b[0] = brow[tx];
+          b[0] = brow[cbase];
         }
+        if (PK) {
+          unsigned long long bp[CP];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float av = e == 0 ? a4[i].x : (e == 1 ? a4[i].y : (e == 2 ? a4[i].z : a4[i].w));
+          for (int c = 0; c < CP; ++c) bp[c] = pack2(b[(2 * c) % CN], b[(2 * c + 1) % CN]);
 #pragma unroll
-          for (int c = 0; c < CN; ++c) acc[i][c] = __fmaf_rn(av, b[c], acc[i][c]);
+          for (int i = 0; i < 8; ++i) {
+            const unsigned long long aa = pack2(a[i][e], a[i][e]);
+#pragma unroll
+            for (int c = 0; c < CP; ++c) ffma2(acc2[i][c], aa, bp[c]);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+#pragma unroll
+            for (int c = 0; c < CN; ++c) acc[i][c] = __fmaf_rn(a[i][e], b[c], acc[i][c]);
+          }
         }
       }
     }
   }
   cp_async_wait<0>();
+  if (PK) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int c = 0; c < CP; ++c) unpack2(acc2[i][c], acc[i][(2 * c) % CN], acc[i][(2 * c + 1) % CN]);
+  }
 
   // ---- epilogue: bias -> activation -> FiLM -> residual -> store
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    const int64_t t = tile_base + ty + 16 * i;  // tile row -> output row
+    const int64_t t = tile_base + rbase + 4 * i;  // tile row -> output row
     if (t >= p.n_out) continue;
     const int64_t o = p.order ? (int64_t)__ldg(p.order + t) : t;
     int64_t frow = o, rrow = o;
@@ -219,7 +275,7 @@ conv_exact_kernel(const ConvParams p) {
     if (p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
 #pragma unroll
     for (int c = 0; c < CN; ++c) {
-      const int col = co_base + ((CN == 8) ? ((c >> 2) * 64 + tx * 4 + (c & 3)) : (tx * CN + c));
+      const int col = co_base + cbase + ((CN == 8) ? ((c >> 2) * 32 + (c & 3)) : c);
       if (col >= p.cout) continue;
       float v = acc[i][c];
       if (p.bias) v = __fadd_rn(v, __ldg(p.bias + col));
@@ -246,24 +302,32 @@ conv_exact_kernel(const ConvParams p) {
   }
 }
 
+template <int TN, bool VEC, bool F2>
+static int launch_exact_v(const ConvParams& p, cudaStream_t st) {
+  const size_t smem = sizeof(ExactSmem<TN>);
+  dim3 grid((unsigned)ceil_div(p.n_out, CE_TM), (unsigned)ceil_div(p.cout, TN));
+  PCC_CHECK_CUDA(cudaFuncSetAttribute(conv_exact_kernel<TN, VEC, F2>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  conv_exact_kernel<TN, VEC, F2><<<grid, CE_THREADS, smem, st>>>(p);
+  PCC_CHECK_LAUNCH("conv_exact_kernel");
+  return PCC_OK;
+}
+
+static bool exact_f2() {
+  static bool f2 = [] {
+    const char* e = getenv("PCC_EXACT_F2");
+    return !(e && atoi(e) == 0);
+  }();
+  return f2;
+}
+
 template <int TN>
 static int launch_exact(const ConvParams& p, cudaStream_t st) {
   const bool vec = (p.cin % 4 == 0) && (p.cout % 4 == 0) &&
                    ((reinterpret_cast<uintptr_t>(p.in) & 15) == 0) &&
                    ((reinterpret_cast<uintptr_t>(p.weight) & 15) == 0);
-  const size_t smem = sizeof(ExactSmem<TN>);
-  dim3 grid((unsigned)ceil_div(p.n_out, CE_TM), (unsigned)ceil_div(p.cout, TN));
-  if (vec) {
-    PCC_CHECK_CUDA(cudaFuncSetAttribute(conv_exact_kernel<TN, true>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    conv_exact_kernel<TN, true><<<grid, CE_THREADS, smem, st>>>(p);
-  } else {
-    PCC_CHECK_CUDA(cudaFuncSetAttribute(conv_exact_kernel<TN, false>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    conv_exact_kernel<TN, false><<<grid, CE_THREADS, smem, st>>>(p);
-  }
-  PCC_CHECK_LAUNCH("conv_exact_kernel");
-  return PCC_OK;
+  if (exact_f2()) return vec ? launch_exact_v<TN, true, true>(p, st) : launch_exact_v<TN, false, true>(p, st);
+  return vec ? launch_exact_v<TN, true, false>(p, st) : launch_exact_v<TN, false, false>(p, st);
 }
 
 int conv_exact(const pcc_conv_args* a, cudaStream_t st) {
@@ -272,7 +336,10 @@ int conv_exact(const pcc_conv_args* a, cudaStream_t st) {
   p.film = a->film; p.film_rows = a->film_rows; p.residual = a->residual; p.res_rows = a->res_rows;
   p.order = a->order; p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
   p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope; p.flags = a->flags;
-  if (a->cout > 64) return launch_exact<128>(p, st);
+  // a grid that cannot fill 2 CTAs on every SM is split further along the output channels
+  const int64_t tiles = ceil_div(p.n_out, CE_TM);
+  const bool small_grid = tiles * ceil_div(p.cout, 128) < 2 * (int64_t)sm_count();
+  if (a->cout > 64 && !small_grid) return launch_exact<128>(p, st);
   if (a->cout > 32) return launch_exact<64>(p, st);
   if (a->cout > 16) return launch_exact<32>(p, st);
   return launch_exact<16>(p, st);

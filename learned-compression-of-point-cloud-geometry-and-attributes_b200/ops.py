@@ -208,12 +208,13 @@ class CoordMap:
             step = -out_map.ts if transpose else self.ts
             align = self.ts if transpose else 1
             ws, wsb = None, 0
-            if K > 1 and n_out > TILE_M and _tile_seg_rows:
+            seg = tile_segment_rows()
+            if K > 1 and n_out > TILE_M and seg:
                 order = torch.empty(n_out, dtype=torch.int32, device=self.device)
                 wsb = _L().pcc_kernel_map_ws_bytes(n_out)
                 ws = _ws(wsb, self.device)
             check(_L().pcc_kernel_map(_ptr(tk), _ptr(tv), cap, _ptr(out_map.keys), n_out, kernel_size, step,
-                                      align, _ptr(nbr), stride, _ptr(tapmask), _ptr(order), _tile_seg_rows,
+                                      align, _ptr(nbr), stride, _ptr(tapmask), _ptr(order), seg,
                                       _ptr(ws), wsb, _stream()), "pcc_kernel_map")
             _count(1 if order is None else 7)
         kmap = KernelMap(nbr, tapmask, K, n_out, stride, order)
@@ -221,14 +222,24 @@ class CoordMap:
         return kmap
 
 
-_tile_seg_rows = 1 << 17  # rows per segment of the tile-row sort (0 = keep lexicographic tiles)
+# Rows per segment of the tile-row sort (0 = keep lexicographic tiles).  None = by mode: the exact
+# (FP32-pipe-bound) path sorts whole maps; the tensor-core path keeps a tile's gathers inside an
+# L2-sized segment of the map.
+_tile_seg_rows = None
 
 
 def set_tile_segment_rows(n):
     """Segment length of the kernel map's tile-row sort (power of two >= 128; 0 disables it).
     Affects only maps built afterwards; results are independent of it."""
     global _tile_seg_rows
-    _tile_seg_rows = int(n)
+    _tile_seg_rows = None if n is None else int(n)
+
+
+def tile_segment_rows():
+    """The segment length in effect for maps built now."""
+    if _tile_seg_rows is not None:
+        return _tile_seg_rows
+    return (1 << 30) if _default_mode == MODE_EXACT else (1 << 17)
 
 
 def make_map(coords_or_keys, ts=1, assume_sorted=False):

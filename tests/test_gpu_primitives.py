@@ -92,6 +92,7 @@ def _oracle_sorted(oracle, c, ts):
 @pytest.mark.parametrize("ks", [1, 2, 3])
 @pytest.mark.parametrize("n,extent,ts", [(60, 6, 1), (7000, 35, 2), (150000, 150, 1)])
 def test_kernel_map_conv(pcc, oracle, ks, n, extent, ts):
+    pcc.ops.set_tile_segment_rows(1 << 16 if n > 100000 else None)  # multi-segment case
     c = random_cloud(n, extent, 6, 1, -3)
     c[:, 1:] *= ts
     m, _ = pcc.ops.canonical_map(torch.from_numpy(c).to(DEV), ts)
@@ -108,7 +109,7 @@ def test_kernel_map_conv(pcc, oracle, ks, n, extent, ts):
     tiled = ref[:, order]
     assert np.array_equal(km.nbr[:, :km.n_out].cpu().numpy(), tiled)
     if km.order is not None:
-        seg = pcc.ops._tile_seg_rows
+        seg = pcc.ops.tile_segment_rows()
         rowmask = ((ref >= 0).astype(np.int64) << np.arange(ref.shape[0])[:, None]).sum(0)
         sortkey = ((np.arange(ref.shape[1]) // seg) << 27) | rowmask
         assert np.array_equal(order, np.argsort(sortkey, kind="stable"))
@@ -125,6 +126,7 @@ def test_kernel_map_conv(pcc, oracle, ks, n, extent, ts):
     km2 = m.kernel_map(s, ks)
     ref2 = oracle.prims.kernel_map(keys, oracle.prims.stride_coords(c, 2 * ts), offs)
     assert np.array_equal(km2.natural_nbr().cpu().numpy(), ref2)
+    pcc.ops.set_tile_segment_rows(None)
 
 
 @pytest.mark.parametrize("ks", [2, 3])
