@@ -8,13 +8,17 @@
 // *published* algorithms and anchors on the reference's call
 // sites, which are cited per function.
 //
-// "parity unpinned": the reference holds no golden vectors, known-answer tests or fixtures
-// for this path.  The pins that do exist are created by this repo:
-//   * tests/test_oracle_conv_dense.py   — sparse conv == torch.nn.functional.conv3d identities
-//   * tests/test_oracle_rans.py         — hand-computed rANS known answers + round trips
-//   * tests/test_oracle_tables.py       — Gaussian tables against scipy.stats.norm
-//   * tests/golden/make_golden.py       — the reference's own model/*.py control flow executed
-//                                         here over these primitives (fixtures committed)
+// "parity unpinned" at the third-party boundary: the reference holds no golden vectors,
+// known-answer tests or fixtures for this path and MinkowskiEngine /
+// CompressAI cannot be run here.  The pins that do exist are created by this repo:
+//   * tests/test_oracle_pins.py  — sparse conv / strided / generative-transposed conv ==
+//                                  torch.nn.functional.conv3d / conv_transpose3d identities,
+//                                  hand-computed rANS known answers + big-int restatement,
+//                                  Gaussian tables against scipy.stats.norm
+//   * tests/golden/make_golden.py + tests/test_golden.py — the reference's OWN model/*.py and
+//                                  utils.py, imported unmodified from /root/reference and executed
+//                                  over these primitives (oracle/ref_shims.py); fixtures committed.
+//                                  Pins control flow and state_dict names, not ME/CompressAI internals.
 //
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
 // may load this library.  The product (csrc/) never links or calls it.

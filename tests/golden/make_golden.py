@@ -1,0 +1,79 @@
+#!/usr/bin/env python
+"""Generates tests/golden/*.npz by running the REFERENCE'S OWN model code.
+
+  python tests/golden/make_golden.py          (in the builder container: needs /root/reference)
+
+/root/reference/model/{model,transforms,blocks,entropy_models}.py and utils.py are imported
+unmodified; the third-party packages they need and that cannot be installed offline
+(MinkowskiEngine, compressai, open3d, bitstream) are replaced by the CPU stand-ins of
+oracle/ref_shims.py, which implement SURVEY.md Appendix A/B over the oracle primitives.  The
+fixtures are therefore outputs of ColorModel.compress / ColorModel.decompress AS WRITTEN IN THE
+REFERENCE (model/model.py:95-208), with the reference's configs/*.yaml, on deterministic synthetic
+weights and inputs.  They pin:  the oracle's control-flow restatement (oracle/codec.py), the
+product's fused plan (codec.py) and the state_dict naming, against the reference's code.
+They do not pin MinkowskiEngine / CompressAI internals (absent; "parity unpinned" there).
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+import yaml
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+REF = "/root/reference"
+
+CASES = [  # name, yaml, product config name, shell radius, seed, (q_g, q_a)
+    ("ours_r14", "configs/Ours.yaml", "OURS_CONFIG", 14.0, 0, (0.5, 0.5)),
+    ("ours_r11_q", "configs/Ours.yaml", "OURS_CONFIG", 11.0, 3, (0.2, 0.9)),
+    ("ablation_r12", "configs/Ablation_NoCondition_Convolution.yaml", "ABLATION_CONFIG", 12.0, 1, (0.75, 0.25)),
+]
+
+
+def main():
+    import pcc_b200
+    from oracle import ref_shims
+    for name, yml, cfg_name, radius, seed, q in CASES:
+        cfg = yaml.safe_load(open(os.path.join(REF, yml)))["model"]
+        assert cfg == getattr(pcc_b200, cfg_name), f"{yml} differs from pcc_b200.{cfg_name}"
+        ref_model = ref_shims.load_reference_model(cfg, REF)
+        # deterministic synthetic weights, taken through the state_dict so key names are pinned
+        ours = pcc_b200.ColorModel(cfg)
+        pcc_b200.init_synthetic(ours, seed)
+        sd = {k: v for k, v in ours.state_dict().items()}
+        missing, unexpected = ref_model.load_state_dict(sd, strict=False)
+        assert not missing, missing          # every parameter of the reference's module tree is supplied
+        assert all(("_offset" in u or "_quantized_cdf" in u or "_cdf_length" in u) for u in unexpected), unexpected
+        ref_model.eval()
+        ref_model.update()
+        x = pcc_b200.synthetic.shell_frame(radius, center=[64, 64, 64], grid=128, seed=seed)
+        qc, qf = pcc_b200.synthetic.uniform_q_map(x, *q)
+        import MinkowskiEngine as ME  # the stand-in
+        with torch.no_grad():
+            Q = ME.SparseTensor(coordinates=qc, features=qf)     # utils.py:436-445
+            strings, shape, k, coordinates = ref_model.compress(x, Q)
+            out = ref_model.decompress(coordinates=coordinates.clone(), strings=strings, shape=shape, k=k)
+        # canonical order for comparison (ME's row order is unspecified)
+        out = out.numpy()
+        key = (out[:, 0].astype(np.int64) << 40) | (out[:, 1].astype(np.int64) << 20) | out[:, 2].astype(np.int64)
+        out = out[np.argsort(key)]
+        coords = coordinates.numpy().astype(np.int32)
+        ck = (coords[:, 1].astype(np.int64) << 40) | (coords[:, 2].astype(np.int64) << 20) | coords[:, 3].astype(np.int64)
+        coords = coords[np.argsort(ck)]
+        np.savez_compressed(
+            os.path.join(HERE, name + ".npz"),
+            config=cfg_name, radius=radius, seed=seed, q=np.array(q, np.float32),
+            x=x.numpy().astype(np.float32),
+            y_string=np.frombuffer(strings[0][0], np.uint8), z_string=np.frombuffer(strings[1][0], np.uint8),
+            shape=np.array(shape, np.int64), k=np.array([int(kk[0]) for kk in k], np.int64),
+            coordinates=coords, out=out.astype(np.float32))
+        print(f"{name}: {x.shape[0]} points, y/z bytes {len(strings[0][0])}/{len(strings[1][0])}, "
+              f"shape {shape}, k {k}, latent voxels {coords.shape[0]}, decoded {out.shape}")
+        for m in [m for m in sys.modules if m == "model" or m.startswith("model.") or m == "utils"]:
+            del sys.modules[m]
+
+
+if __name__ == "__main__":
+    main()
