@@ -112,7 +112,7 @@ def frame_for(rank, step, world, radius):
     import pcc_b200
     if world == 1:
         return pcc_b200.synthetic.shell_frame(radius, seed=0)
-    t = step * world + rank
+    t = pcc_b200.frames.frames_of_rank((step + 1) * world, rank, world)[step]  # = step * world + rank
     import numpy as np
     r = radius + 4.0 * np.sin(2.0 * np.pi * t / 300.0)
     return pcc_b200.synthetic.shell_frame(r, seed=t)
@@ -320,15 +320,7 @@ def run_ours(args, rank, world, local_rank):
     d2h += cc.coder_stats["d2h_bytes"]
 
     # ---- max over ranks
-    if world > 1:
-        t = torch.tensor([t_dev, t_e2e], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        t_dev, t_e2e = t.tolist()
-        n = torch.tensor([npts], device=dev, dtype=torch.float64)
-        dist.all_reduce(n, op=dist.ReduceOp.SUM)
-        npts_all = int(n.item())
-    else:
-        npts_all = npts
+    (t_dev, t_e2e), npts_all = pcc_b200.frames.reduce_throughput([t_dev, t_e2e], npts, dev)
     if rank != 0:
         return
 
