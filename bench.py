@@ -280,6 +280,9 @@ def run_ours(args, rank, world, local_rank):
             dev_inputs.append(dev_inputs[0])
     for s in range(args.warmup):
         step_device(*dev_inputs[s])
+    import gc
+    gc.collect()
+    gc.disable()  # no collector pauses inside the timed regions (re-enabled after the e2e loop)
     barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -289,9 +292,12 @@ def run_ours(args, rank, world, local_rank):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     npts = 0
+    step_wall = []
     for s in range(args.warmup, total):
+        tw = time.perf_counter()
         out = step_device(*dev_inputs[s])
         npts += out.shape[0]
+        step_wall.append(round((time.perf_counter() - tw) * 1e3, 2))
     ev1.record()
     barrier()
     t_dev = ev0.elapsed_time(ev1) * 1e-3
@@ -308,14 +314,18 @@ def run_ours(args, rank, world, local_rank):
     e0.record()
     t0 = time.perf_counter()
     h2d = d2h = 0
+    step_wall_e2e = []
     for s in range(args.warmup, total):
         xh, qch, qfh = host_inputs(s)
+        tw = time.perf_counter()
         out, c_host = step_e2e(xh, qch, qfh)
+        step_wall_e2e.append(round((time.perf_counter() - tw) * 1e3, 2))
         h2d += xh.numel() * 4 + qch.numel() * 4 + qfh.numel() * 4 + c_host.numel() * 4
         d2h += out.numel() * 4 + c_host.numel() * 4
     e1.record()
     barrier()
     t_e2e = max(e0.elapsed_time(e1) * 1e-3, time.perf_counter() - t0)
+    gc.enable()
     h2d += cc.coder_stats["h2d_bytes"]
     d2h += cc.coder_stats["d2h_bytes"]
 
@@ -353,6 +363,9 @@ def run_ours(args, rank, world, local_rank):
                   "symbols_per_step": coder["symbols"] // args.steps,
                   "note": "reference's sequential CPU rANS, inside ms_per_step; value_excl_coder removes it"},
         "value_excl_coder": npts_all / max(t_dev - coder["encode_s"] - coder["decode_s"], 1e-9),
+        "step_host_ms": {"device_resident": step_wall, "e2e": step_wall_e2e,
+                         "note": "host wall clock per step on rank 0 (launch side; the decoded cloud's "
+                                 "D2H ends each e2e step)"},
     }
     if roof is not None:
         line["roofline"] = roof

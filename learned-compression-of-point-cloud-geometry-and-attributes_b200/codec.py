@@ -23,6 +23,28 @@ from ._lib import PccError
 
 RELU, LEAKY, NONE = ops.ACT_RELU, ops.ACT_LEAKY, ops.ACT_NONE
 
+# Optional stage timer (tools/stage_profile.py): when set to a dict, every `with stage(name)` block
+# is bracketed by device synchronisations and its wall time accumulated.  Off (None) on the hot path.
+STAGE_MS = None
+
+
+class stage:
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if STAGE_MS is not None:
+            import time
+            torch.cuda.synchronize()
+            self.t0 = time.perf_counter()
+
+    def __exit__(self, *exc):
+        if STAGE_MS is not None:
+            import time
+            torch.cuda.synchronize()
+            STAGE_MS[self.name] = STAGE_MS.get(self.name, 0.0) + (time.perf_counter() - self.t0) * 1e3
+        return False
+
 
 def _conv(cin, cout, k=3, stride=1, bias=True):
     return ME.MinkowskiConvolution(in_channels=cin, out_channels=cout, kernel_size=k, stride=stride,
@@ -327,20 +349,24 @@ class SparseSynthesisTransform(nn.Module):
         self.down_conv = ME.MinkowskiConvolution(in_channels=1, out_channels=1, kernel_size=3, stride=2, dimension=3)
 
     def forward(self, x, Q, coords=None, k=None, full_predictions=False):
-        if self.cond_conv is not None:
-            Q_plus = seq3(x, self.cond_conv)
-            Q = ST(ops.gather_rows(Q_plus.F, rows_of(x.m, Q.m), add=Q.F), Q.m)  # (:258-265)
-        x = apply_conv(x, self.pre_conv[0], act=RELU)
-        Q = seq5(Q, self.q_pre_conv)
+        with stage("g_s.pre"):
+            if self.cond_conv is not None:
+                Q_plus = seq3(x, self.cond_conv)
+                Q = ST(ops.gather_rows(Q_plus.F, rows_of(x.m, Q.m), add=Q.F), Q.m)  # (:258-265)
+            x = apply_conv(x, self.pre_conv[0], act=RELU)
+            Q = seq5(Q, self.q_pre_conv)
         predictions = []
         for s in (1, 2, 3):
-            beta_gamma = seq5(Q, getattr(self, f"q_predict_{s}"))
-            x = getattr(self, f"scale_{s}")(x, beta_gamma)
-            x, pred, up_map = getattr(self, f"up_{s}")(x, k=k[s - 1], full_predictions=full_predictions)
-            Q = getattr(self, f"q_up_{s}")(Q, up_map)
-            Q = ST(Q.F, x.m)  # same coordinates after pruning: share the map object with x
+            with stage(f"g_s.stage{s}.q_predict+scale"):
+                beta_gamma = seq5(Q, getattr(self, f"q_predict_{s}"))
+                x = getattr(self, f"scale_{s}")(x, beta_gamma)
+            with stage(f"g_s.stage{s}.up"):
+                x, pred, up_map = getattr(self, f"up_{s}")(x, k=k[s - 1], full_predictions=full_predictions)
+                Q = getattr(self, f"q_up_{s}")(Q, up_map)
+                Q = ST(Q.F, x.m)  # same coordinates after pruning: share the map object with x
             predictions.append(pred)
-        x = seq5(x, self.post_conv)
+        with stage("g_s.post"):
+            x = seq5(x, self.post_conv)
         if coords is not None:
             p1 = coords.m.stride2()
             p2 = p1.stride2()
@@ -410,13 +436,17 @@ class MeanScaleHyperprior_Map(CompressionModel):
 
     def compress(self, y):
         """(:341-381).  y is canonical already, so sort_tensor (:346-347) is the identity."""
-        z = self.run_h_a(y)
+        with stage("enc.h_a"):
+            z = self.run_h_a(y)
         shape = [z.m.n]
-        z_sym, z_hat_f = self.entropy_bottleneck.quantize_rows(z.F)
-        z_string = self.entropy_bottleneck.compress_symbols(z_sym)
+        with stage("enc.z_coder"):
+            z_sym, z_hat_f = self.entropy_bottleneck.quantize_rows(z.F)
+            z_string = self.entropy_bottleneck.compress_symbols(z_sym)
         z_hat = ST(z_hat_f, z.m)  # == decompress(compress(z)) (:352-353): the coder is lossless
-        params = self.run_h_s(z_hat, at_map=y.m)
-        y_string, y_sym, y_idx = self.gaussian_conditional.compress_fused(y.F, params.F, None)
+        with stage("enc.h_s"):
+            params = self.run_h_s(z_hat, at_map=y.m)
+        with stage("enc.y_coder"):
+            y_string, y_sym, y_idx = self.gaussian_conditional.compress_fused(y.F, params.F, None)
         self.last = {"z": z, "z_hat": z_hat, "params": params, "y_symbols": y_sym, "indexes": y_idx,
                      "z_symbols": z_sym}
         return [y.m, z.m], [[y_string], [z_string]], shape
@@ -424,12 +454,15 @@ class MeanScaleHyperprior_Map(CompressionModel):
     def decompress(self, points, strings, shape):
         """(:384-414).  points = [y map, z map], both canonical (sort_points, :389-390)."""
         y_map, z_map = points
-        z_hat_cn = self.entropy_bottleneck.decompress(strings[1], shape)
-        z_hat = ST(z_hat_cn[0].t().contiguous(), z_map)
-        Q_hat = self.run_h_q(z_hat)
-        params = self.run_h_s(z_hat, at_map=y_map)
-        y_hat_f = self.gaussian_conditional.decompress_fused(strings[0][0], params.F, None, y_map.n,
-                                                             params.F.shape[1] // 2)
+        with stage("dec.z_coder"):
+            z_hat_cn = self.entropy_bottleneck.decompress(strings[1], shape)
+            z_hat = ST(z_hat_cn[0].t().contiguous(), z_map)
+        with stage("dec.h_q+h_s"):
+            Q_hat = self.run_h_q(z_hat)
+            params = self.run_h_s(z_hat, at_map=y_map)
+        with stage("dec.y_coder"):
+            y_hat_f = self.gaussian_conditional.decompress_fused(strings[0][0], params.F, None, y_map.n,
+                                                                 params.F.shape[1] // 2)
         self.last = {"z_hat": z_hat, "params": params}
         return ST(y_hat_f, y_map), Q_hat
 
@@ -517,8 +550,10 @@ class ColorModel(CompressionModel):
     @torch.no_grad()
     def compress(self, x, Q, path=None):
         """model/model.py:95-147, in-memory variant: returns (strings, shape, k, coordinates)."""
-        inp, Qt = self._inputs(x, Q)
-        y, Qy, k = self.g_a(inp, Qt)
+        with stage("enc.inputs"):
+            inp, Qt = self._inputs(x, Q)
+        with stage("enc.g_a"):
+            y, Qy, k = self.g_a(inp, Qt)
         if self.entropy_model_map is None:
             points, strings, shape = self.entropy_model.compress(y)
         else:
@@ -546,8 +581,9 @@ class ColorModel(CompressionModel):
                                                  dtype=coordinates.dtype), coordinates], dim=1)
         if coordinates.is_floating_point():
             coordinates = torch.floor(coordinates)
-        y_map, _ = ops.canonical_map(coordinates.int(), 8)
-        z_map = y_map.stride2().stride2()  # g_s.down_conv twice, only .C is used (:188-191)
+        with stage("dec.maps"):
+            y_map, _ = ops.canonical_map(coordinates.int(), 8)
+            z_map = y_map.stride2().stride2()  # g_s.down_conv twice, only .C is used (:188-191)
         if self.entropy_model_map is None:
             y_hat, Q_hat = self.entropy_model.decompress([y_map, z_map], strings, shape)
         else:
@@ -556,7 +592,8 @@ class ColorModel(CompressionModel):
         self.last = {"y_hat": y_hat, "Q_hat": Q_hat}
         x_hat = self.g_s(y_hat, Q_hat, k=k)
         self.last["x_hat"] = x_hat
-        return ops.color_finalize(x_hat.m.keys, x_hat.F)  # (:206-207)
+        with stage("dec.finalize"):
+            return ops.color_finalize(x_hat.m.keys, x_hat.F)  # (:206-207)
 
 
 # ------------------------------------------------------------------------------------------

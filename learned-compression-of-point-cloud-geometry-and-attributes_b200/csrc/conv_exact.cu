@@ -70,12 +70,12 @@ __device__ __forceinline__ void ffma2(unsigned long long& d, unsigned long long 
   asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
 }
 
-template <int TN, bool VEC, bool F2>
+template <int TN, bool VEC, int F2>
 __global__ void __launch_bounds__(CE_THREADS, 2)
 conv_exact_kernel(const ConvParams p) {
   constexpr int CN = TN / 16;  // output channels per thread
   constexpr int AV = 4;        // floats of a gathered row per shared-memory load (LDS.128)
-  constexpr bool PK = F2 && (CN % 2 == 0);
+  constexpr bool PK = (F2 != 0) && (CN % 2 == 0);
   constexpr int CP = PK ? CN / 2 : 1;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   ExactSmem<TN>& sm = *reinterpret_cast<ExactSmem<TN>*>(smem_raw);
@@ -302,7 +302,7 @@ conv_exact_kernel(const ConvParams p) {
   }
 }
 
-template <int TN, bool VEC, bool F2>
+template <int TN, bool VEC, int F2>
 static int launch_exact_v(const ConvParams& p, cudaStream_t st) {
   const size_t smem = sizeof(ExactSmem<TN>);
   dim3 grid((unsigned)ceil_div(p.n_out, CE_TM), (unsigned)ceil_div(p.cout, TN));
@@ -313,10 +313,10 @@ static int launch_exact_v(const ConvParams& p, cudaStream_t st) {
   return PCC_OK;
 }
 
-static bool exact_f2() {
-  static bool f2 = [] {
+static int exact_f2() {
+  static int f2 = [] {
     const char* e = getenv("PCC_EXACT_F2");
-    return !(e && atoi(e) == 0);
+    return e ? atoi(e) : 1;
   }();
   return f2;
 }
@@ -326,8 +326,9 @@ static int launch_exact(const ConvParams& p, cudaStream_t st) {
   const bool vec = (p.cin % 4 == 0) && (p.cout % 4 == 0) &&
                    ((reinterpret_cast<uintptr_t>(p.in) & 15) == 0) &&
                    ((reinterpret_cast<uintptr_t>(p.weight) & 15) == 0);
-  if (exact_f2()) return vec ? launch_exact_v<TN, true, true>(p, st) : launch_exact_v<TN, false, true>(p, st);
-  return vec ? launch_exact_v<TN, true, false>(p, st) : launch_exact_v<TN, false, false>(p, st);
+  const int f2 = exact_f2();
+  if (f2 != 0) return vec ? launch_exact_v<TN, true, 1>(p, st) : launch_exact_v<TN, false, 1>(p, st);
+  return vec ? launch_exact_v<TN, true, 0>(p, st) : launch_exact_v<TN, false, 0>(p, st);
 }
 
 int conv_exact(const pcc_conv_args* a, cudaStream_t st) {

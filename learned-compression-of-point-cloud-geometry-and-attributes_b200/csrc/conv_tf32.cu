@@ -20,6 +20,9 @@
 //
 // Roofline: tensor pipe (tf32 dense) for cin, cout >= 64; the gather (128 B per row per step from
 // L2) is the competing bound, see DESIGN.md.
+#include <cuda.h>
+#include <stdlib.h>
+
 #include "pcc_common.cuh"
 
 namespace pcc {
@@ -115,6 +118,24 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
 }
 
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n}\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_gather4(uint32_t dst, const void* desc, uint32_t bar, int c0, int r0, int r1,
+                                            int r2, int r3) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile::gather4.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];\n" ::"r"(dst), "l"(desc), "r"(bar), "r"(c0), "r"(r0), "r"(r1), "r"(r2),
+      "r"(r3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* desc, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];\n" ::"r"(dst), "l"(desc), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+
 // K-major, SWIZZLE_128B shared-memory matrix descriptor (sm_100 encoding):
 //   [0,14) start address >> 4, [16,30) leading byte offset >> 4 (unused for swizzled K-major),
 //   [32,46) stride byte offset >> 4 (1024 B between 8-row atoms), [46,48) version = 1,
@@ -151,7 +172,7 @@ struct TcSmem {
 
 template <int BN>
 __global__ void __launch_bounds__(TC_THREADS, 2)
-conv_tf32_kernel(const TcParams p) {
+conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
   extern __shared__ unsigned char smem_raw[];
   // 1024-byte alignment for the swizzle atoms
   const uint32_t raw = smem_u32(smem_raw);
@@ -177,7 +198,7 @@ conv_tf32_kernel(const TcParams p) {
 
   if (tid == 0) {
     for (int s = 0; s < TC_STAGES; ++s) {
-      mbar_init(full_bar(s), TC_PRODUCERS);
+      mbar_init(full_bar(s), TC_PRODUCERS + 1);  // 128 gather arrivals + the weight tile's expect_tx
       mbar_init(empty_bar(s), 1);
     }
     mbar_init(accum_bar, 1);
@@ -211,33 +232,37 @@ conv_tf32_kernel(const TcParams p) {
     int pk = pmask ? (__ffs(pmask) - 1) : 0;
     int pa = 0;  // ordinal of pk among the active offsets
     int pchunk = 0;
-    int idx[8];
+    // per offset: source pointer of this thread's 16-byte chunk in each of its 8 rows (nullptr =
+    // missing neighbour -> zero fill); per step only the channel-chunk displacement is added.
+    // Destination: rows rbase + 16 j share (row & 7), so the swizzled offset is off0 + 2048 j.
+    const char* rowp[8];
     bool need_idx = true;
+    const uint32_t off0 = sw128_offset(rbase, chunk);
+    const char* in_b = reinterpret_cast<const char*>(p.in) + chunk * 16;
+    const int64_t row_bytes = (int64_t)p.cin * 4;
     for (int s = 0; s < nsteps; ++s) {
       const int stage = s % TC_STAGES;
       if (s >= TC_STAGES) mbar_wait(empty_bar(stage), (uint32_t)(((s / TC_STAGES) - 1) & 1));
       if (need_idx) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) idx[j] = s_nbr[pa * TC_TM + rbase + 16 * j];
+        for (int j = 0; j < 8; ++j) {
+          const int ix = s_nbr[pa * TC_TM + rbase + 16 * j];
+          rowp[j] = ix >= 0 ? in_b + ix * row_bytes : nullptr;
+        }
         need_idx = false;
       }
       const uint32_t a_stage = base + stage * S::STAGE_BYTES;
       const uint32_t b_stage = a_stage + S::A_BYTES;
-      const int ci = pchunk * TC_TK + chunk * 4;
+      const int cdisp = pchunk * (TC_TK * 4);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const int r = rbase + 16 * j;
-        const bool ok = idx[j] >= 0;
-        const float* src = ok ? p.in + (int64_t)idx[j] * p.cin + ci : p.in;
-        tc_cp_async16(a_stage + sw128_offset(r, chunk), src, ok ? 16 : 0);
+        const bool ok = rowp[j] != nullptr;
+        tc_cp_async16(a_stage + off0 + 2048u * j, ok ? rowp[j] + cdisp : reinterpret_cast<const char*>(p.in), ok ? 16 : 0);
       }
-      const float* wk = p.weight_t + ((int64_t)pk * p.cout + co_base) * p.cin + ci;
-#pragma unroll
-      for (int j = 0; j < BN / 16; ++j) {
-        const int r = rbase + 16 * j;  // weight row = output channel co_base + r
-        const bool ok = co_base + r < p.cout;
-        const float* src = ok ? wk + (int64_t)r * p.cin : p.weight_t;
-        tc_cp_async16(b_stage + sw128_offset(r, chunk), src, ok ? 16 : 0);
+      // weight slice Wt[pk][co_base .. +BN][ci chunk]: one tiled TMA load (SWIZZLE_128B box) by one thread
+      if (tid == 0) {
+        mbar_expect_tx(full_bar(stage), (uint32_t)S::B_BYTES);
+        tma_load_2d(b_stage, &tm_b, full_bar(stage), pchunk * TC_TK, pk * p.cout + co_base);
       }
       tc_cp_commit();
       if (s >= TC_LAG) {
@@ -347,14 +372,268 @@ conv_tf32_kernel(const TcParams p) {
   if (warp == 4) tmem_dealloc(tmem_acc, TMEM_COLS);
 }
 
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      f = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(f);
+  }();
+  return fn;
+}
+
+// 2-D fp32 tensor [rows x cols] (row-major), box = box_rows x 32 columns (128 B), SWIZZLE_128B
+static int make_map_2d(CUtensorMap* m, const float* ptr, int64_t rows, int64_t cols, int box_rows) {
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled is not available from the driver");
+    return PCC_ERR_CUDA;
+  }
+  const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t gstr[1] = {(cuuint64_t)cols * 4};
+  const cuuint32_t box[2] = {32u, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1u, 1u};
+  const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), gdim, gstr, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d) for a [%lld x %lld] tensor", (int)r, (long long)rows, (long long)cols);
+    return PCC_ERR_CUDA;
+  }
+  return PCC_OK;
+}
+
 template <int BN>
 static int launch_tc(const TcParams& p, cudaStream_t st) {
+  CUtensorMap tm_b;
+  const int rc = make_map_2d(&tm_b, p.weight_t, (int64_t)p.K * p.cout, p.cin, BN);
+  if (rc) return rc;
   const size_t smem = TcSmem<BN>::TOTAL;
   PCC_CHECK_CUDA(cudaFuncSetAttribute(conv_tf32_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((unsigned)ceil_div(p.n_out, TC_TM), (unsigned)ceil_div(p.cout, BN));
-  conv_tf32_kernel<BN><<<grid, TC_THREADS, smem, st>>>(p);
+  conv_tf32_kernel<BN><<<grid, TC_THREADS, smem, st>>>(tm_b, p);
   PCC_CHECK_LAUNCH("conv_tf32_kernel");
   return PCC_OK;
+}
+
+// ======================================================================================
+// TMA variant: the gathered operand rows are fetched by cp.async.bulk.tensor ... tile::gather4
+// (one instruction = four rows of the feature map by row index, 128 B each, zero-filled when the
+// index is out of bounds — which is how a missing neighbour, index -1, becomes a zero row), the
+// weight slice by a plain 2-D tiled TMA load; both land in the SWIZZLE_128B layout the UMMA
+// descriptors expect and complete on the stage's mbarrier (expect_tx), so there are no per-thread
+// copies, address arithmetic, cp.async waits or proxy fences left:
+//   warp 0   producer: per step one elected lane arms the barrier, then each of the 32 lanes issues
+//            one gather4 (rows 4 lane .. 4 lane + 3 of the tile) and lane 0 the weight tile
+//   warp 1   lane 0 issues tcgen05.mma and commits the stage / accumulator barriers
+//   warps 2-5 epilogue (TMEM lanes 32 (warp % 4) ..), fused bias / activation / FiLM / residual
+constexpr int TM_THREADS = 192;
+constexpr int TM_STAGES = 3;
+
+template <int BN>
+struct TmSmem {
+  static constexpr int A_BYTES = TC_TM * 128;
+  static constexpr int B_BYTES = BN * 128;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int BAR_OFFSET = TM_STAGES * STAGE_BYTES;
+  static constexpr int NBR_OFFSET = BAR_OFFSET + 128;
+  static constexpr int TOTAL = NBR_OFFSET + 27 * TC_TM * 4 + 1024;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(TM_THREADS, 2)
+conv_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  unsigned char* sbase = smem_raw + (base - raw);
+  using S = TmSmem<BN>;
+  const uint32_t bar_base = base + S::BAR_OFFSET;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (TM_STAGES + s); };
+  const uint32_t accum_bar = bar_base + 8u * (2 * TM_STAGES);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * TM_STAGES + 1);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(sbase + S::BAR_OFFSET + 8 * (2 * TM_STAGES + 1));
+  int32_t* s_nbr = reinterpret_cast<int32_t*>(sbase + S::NBR_OFFSET);
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int64_t tile_base = (int64_t)blockIdx.x * TC_TM;
+  const int co_base = blockIdx.y * BN;
+  const int nchunks = p.cin / TC_TK;
+  const uint32_t kfull = p.K >= 32 ? 0xffffffffu : ((1u << p.K) - 1u);
+  const uint32_t mask = p.tapmask ? (p.tapmask[blockIdx.x] & kfull) : kfull;
+  const int nact = __popc(mask);
+  const int nsteps = nact * nchunks;
+  constexpr uint32_t TMEM_COLS = BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256));
+
+  if (tid == 0) {
+    for (int s = 0; s < TM_STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    mbar_init(accum_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  for (int a = warp; a < nact; a += TM_THREADS / 32) {
+    const int k = __fns(mask, 0, a + 1);
+#pragma unroll
+    for (int r = lane; r < TC_TM; r += 32) {
+      const int64_t t = tile_base + r;
+      s_nbr[a * TC_TM + r] = (t < p.n_out) ? __ldg(p.nbr + (int64_t)k * p.nbr_stride + t) : -1;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_acc = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ============================ TMA producer ============================
+    uint32_t pmask = mask;
+    int pk = pmask ? (__ffs(pmask) - 1) : 0;
+    int pa = 0, pchunk = 0;
+    int4 rows = make_int4(-1, -1, -1, -1);
+    bool need_idx = true;
+    const uint32_t a_off = (uint32_t)((lane >> 1) * 1024 + (lane & 1) * 512);  // tile rows 4 lane .. 4 lane + 3
+    for (int s = 0; s < nsteps; ++s) {
+      const int stage = s % TM_STAGES;
+      if (s >= TM_STAGES) mbar_wait(empty_bar(stage), (uint32_t)(((s / TM_STAGES) - 1) & 1));
+      if (need_idx) {
+        rows = *reinterpret_cast<const int4*>(s_nbr + pa * TC_TM + 4 * lane);
+        need_idx = false;
+      }
+      const uint32_t a_stage = base + stage * S::STAGE_BYTES;
+      if (lane == 0) mbar_expect_tx(full_bar(stage), (uint32_t)S::STAGE_BYTES);
+      __syncwarp();
+      tma_gather4(a_stage + a_off, &tm_a, full_bar(stage), pchunk * TC_TK, rows.x, rows.y, rows.z, rows.w);
+      if (lane == 0)
+        tma_load_2d(a_stage + S::A_BYTES, &tm_b, full_bar(stage), pchunk * TC_TK, pk * p.cout + co_base);
+      if (++pchunk == nchunks) {
+        pchunk = 0;
+        pmask &= pmask - 1;
+        pk = pmask ? (__ffs(pmask) - 1) : 0;
+        ++pa;
+        need_idx = true;
+      }
+    }
+  } else if (warp == 1) {
+    // ============================ MMA issuer (one elected lane) ============================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_tf32(TC_TM, BN);
+      for (int s = 0; s < nsteps; ++s) {
+        const int stage = s % TM_STAGES;
+        mbar_wait(full_bar(stage), (uint32_t)((s / TM_STAGES) & 1));
+        tc_fence_after();
+        const uint32_t a_stage = base + stage * S::STAGE_BYTES;
+        const uint32_t b_stage = a_stage + S::A_BYTES;
+#pragma unroll
+        for (int kk = 0; kk < TC_TK / 8; ++kk) {
+          const uint64_t da = make_sw128_desc(a_stage + kk * 32);
+          const uint64_t db = make_sw128_desc(b_stage + kk * 32);
+          umma_tf32(tmem_acc, da, db, idesc, (s > 0 || kk > 0) ? 1u : 0u);
+        }
+        umma_commit(empty_bar(stage));
+      }
+      umma_commit(accum_bar);
+    }
+    __syncwarp();
+  } else {
+    // ============================ epilogue (warps 2-5 own TMEM lanes 32 (warp % 4) ..) ============================
+    const int q = warp & 3;
+    if (nsteps > 0) {
+      mbar_wait(accum_bar, 0);
+      tc_fence_after();
+    }
+    const int64_t t = tile_base + q * 32 + lane;  // tile row -> output row
+    const bool live = t < p.n_out;
+    const int64_t o = (live && p.order) ? (int64_t)__ldg(p.order + t) : t;
+    int64_t frow = o, rrow = o;
+    if (live && p.film_c && p.film_rows) frow = __ldg(p.film_rows + o);
+    if (live && p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
+    const bool vec4 = (p.out_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32) {
+      if (co_base + c0 >= p.cout) break;  // warp-uniform
+      uint32_t v[32];
+      if (nsteps > 0) {
+        tmem_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = 0u;
+      }
+      if (live) {
+        float r[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const int col = co_base + c0 + i;
+          float x = __uint_as_float(v[i]);
+          if (col < p.cout) {
+            if (p.bias) x = __fadd_rn(x, __ldg(p.bias + col));
+            if (p.act == PCC_ACT_RELU)
+              x = fmaxf(x, 0.0f);
+            else if (p.act == PCC_ACT_LEAKY)
+              x = x > 0.0f ? x : __fmul_rn(x, p.slope);
+            if (p.film_c) {
+              float beta = 0.0f, gamma = 0.0f;
+              if (frow >= 0) {
+                const int fc = p.film_c == 1 ? 0 : col;
+                beta = __ldg(p.film + frow * 2 * p.film_c + fc);
+                gamma = __ldg(p.film + frow * 2 * p.film_c + p.film_c + fc);
+              }
+              x = __fadd_rn(__fmul_rn(x, beta), gamma);
+            }
+            if (p.residual) x = __fadd_rn(x, rrow >= 0 ? __ldg(p.residual + rrow * p.cout + col) : 0.0f);
+            if (p.flags & PCC_CONV_ROUND_OUT_TF32) x = round_tf32(x);
+          }
+          r[i] = x;
+        }
+        float* dst = p.out + o * p.out_stride + co_base + c0;
+        if (vec4 && co_base + c0 + 32 <= p.cout) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 4)
+            *reinterpret_cast<float4*>(dst + i) = make_float4(r[i], r[i + 1], r[i + 2], r[i + 3]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (co_base + c0 + i < p.cout) dst[i] = r[i];
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_acc, TMEM_COLS);
+}
+
+template <int BN>
+static int launch_tma(const TcParams& p, int64_t n_in, cudaStream_t st) {
+  CUtensorMap tm_a, tm_b;
+  int rc = make_map_2d(&tm_a, p.in, n_in, p.cin, 1);
+  if (rc) return rc;
+  rc = make_map_2d(&tm_b, p.weight_t, (int64_t)p.K * p.cout, p.cin, BN);
+  if (rc) return rc;
+  const size_t smem = TmSmem<BN>::TOTAL;
+  PCC_CHECK_CUDA(cudaFuncSetAttribute(conv_tma_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid((unsigned)ceil_div(p.n_out, TC_TM), (unsigned)ceil_div(p.cout, BN));
+  conv_tma_kernel<BN><<<grid, TM_THREADS, smem, st>>>(tm_a, tm_b, p);
+  PCC_CHECK_LAUNCH("conv_tma_kernel");
+  return PCC_OK;
+}
+
+static bool use_tma() {
+  static bool v = [] {
+    const char* e = getenv("PCC_TF32_TMA");
+    return e && atoi(e) == 1;  // measured 1.6x slower than the cp.async gather: off by default
+  }();
+  return v;
 }
 
 bool conv_tf32_supported(const pcc_conv_args* a) {
@@ -368,6 +647,11 @@ int conv_tf32(const pcc_conv_args* a, cudaStream_t st) {
   p.film = a->film; p.film_rows = a->film_rows; p.residual = a->residual; p.res_rows = a->res_rows;
   p.order = a->order; p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
   p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope; p.flags = a->flags;
+  if (use_tma() && a->n_in > 0) {
+    if (a->cout > 64) return launch_tma<128>(p, a->n_in, st);
+    if (a->cout > 32) return launch_tma<64>(p, a->n_in, st);
+    return launch_tma<32>(p, a->n_in, st);
+  }
   if (a->cout % 128 == 0 || a->cout > 128) return launch_tc<128>(p, st);
   if (a->cout > 64) return launch_tc<128>(p, st);
   if (a->cout > 32) return launch_tc<64>(p, st);

@@ -362,7 +362,10 @@ __global__ void color_finalize_kernel(const uint64_t* __restrict__ keys, const f
   float* o = out + i * (3 + c);
   o[0] = (float)x; o[1] = (float)y; o[2] = (float)z;
   for (int j = 0; j < c; ++j) {
-    const float q = fminf(fmaxf(rintf(__fmul_rn(feats[i * c + j], 255.0f)), 0.0f), 255.0f);
+    // torch.clamp(torch.round(F * 255), 0.0, 255.0) / 255 (model/model.py:206): comparisons, not
+    // fmaxf/fminf, so that round(-0.3) = -0.0 stays -0.0 exactly as torch.clamp leaves it
+    const float r = rintf(__fmul_rn(feats[i * c + j], 255.0f));
+    const float q = r < 0.0f ? 0.0f : (r > 255.0f ? 255.0f : r);
     o[3 + j] = __fdiv_rn(q, 255.0f);
   }
 }
