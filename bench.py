@@ -41,6 +41,11 @@ def parse_args():
     ap.add_argument("--config", default="ours", choices=["ours", "ablation"])
     ap.add_argument("--q", type=float, nargs=2, default=[0.5, 0.5], metavar=("Q_G", "Q_A"))
     ap.add_argument("--dump-layers", default=None, help="write the per-layer conv timing table here")
+    ap.add_argument("--frames-per-step", type=int, default=6,
+                    help="frames coded per step per GPU (frame pipeline; 1 = one frame at a time)")
+    ap.add_argument("--depth", type=int, default=3, help="frames in flight per GPU")
+    ap.add_argument("--no-tf32-pass", action="store_true",
+                    help="skip the secondary tensor-core (tf32) measurement added to the exact-mode line")
     return ap.parse_args()
 
 
@@ -209,6 +214,36 @@ def roofline_pass(model, x_dev, q_dev, peaks, clocks, dump=None):
     return roof, recs
 
 
+def tf32_pass(args, model, dev, frame_dev, B, peaks, clocks):
+    """Secondary measurement in the tensor-core mode (tcgen05 kind::tf32 for every layer with
+    Cin, Cout multiples of 32), same workload and pipeline; N = 1 only.  Not the parity mode: latents
+    agree with the exact mode to the tolerance stated in tests/test_gpu_tf32.py."""
+    import torch
+    import pcc_b200
+    ops = pcc_b200.ops
+    ops.set_default_mode(ops.MODE_TF32)
+    try:
+        pipe = pcc_b200.pipeline.FramePipeline(model, depth=min(args.depth, B), device=dev)
+        steps, warm = 3, 2
+        for _ in range(warm):
+            pipe.roundtrip_many([frame_dev] * B)
+        torch.cuda.synchronize()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        npts = 0
+        for _ in range(steps):
+            npts += sum(o.shape[0] for o, _, _ in pipe.roundtrip_many([frame_dev] * B))
+        ev1.record()
+        torch.cuda.synchronize()
+        t = ev0.elapsed_time(ev1) * 1e-3
+        roof, _ = roofline_pass(model, *frame_dev, peaks, clocks, None)
+        return {"value": npts / t, "unit": UNIT, "ms_per_frame": t / (steps * B) * 1e3, "steps": steps,
+                "warmup": warm, "dtype": "tf32", "roofline": roof,
+                "note": "tcgen05.mma kind::tf32 path, same frames and pipeline; tolerance mode, not bit-exact"}
+    finally:
+        ops.set_default_mode(ops.MODE_EXACT)
+
+
 def cpu_baseline(args, cfg_name):
     """Oracle (kind "port") timed on the host cores on a bounded sample (rank 0, N=1 only)."""
     import pcc_b200
@@ -244,9 +279,13 @@ def run_ours(args, rank, world, local_rank):
         pass
 
     total = args.warmup + args.steps
-    frames = [frame_for(rank, s, world, args.radius) for s in range(total if world > 1 else 1)]
+    B = max(1, args.frames_per_step)
+    # world == 1: the configs[1] frame, B copies per step; world > 1: rank r codes frames r, r + W, ...
+    # of the synthetic sequence (configs[3]), B distinct frames per step
+    frames = [frame_for(rank, s, world, args.radius) for s in range(total * B if world > 1 else 1)]
     get = (lambda s: frames[s]) if world > 1 else (lambda s: frames[0])
     qmaps = {}
+    pipe = pcc_b200.pipeline.FramePipeline(model, depth=min(args.depth, B), device=dev)
 
     def host_inputs(s):
         x = get(s)
@@ -260,26 +299,30 @@ def run_ours(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step_device(xd, qd):
-        s, sh, k, c = model.compress(xd, qd)
-        return model.decompress(coordinates=c, strings=s, shape=sh, k=k)
+    def step_device(s):
+        """B frames already resident in HBM through the frame pipeline -> points coded."""
+        res = pipe.roundtrip_many([dev_inputs[s * B + j] for j in range(B)])
+        return sum(o.shape[0] for o, _, _ in res)
 
-    def step_e2e(xh, qch, qfh):
-        s, sh, k, c = model.compress(xh, (qch, qfh))            # H2D of the frame inside
-        c_host = c.cpu()                                          # latent coordinates leave the device
-        out = model.decompress(coordinates=c_host, strings=s, shape=sh, k=k)
-        return out.cpu(), c_host
+    def step_e2e(s):
+        """B frames from pinned host memory; latent coordinates and decoded clouds back on the host."""
+        ins = [host_inputs(s * B + j) for j in range(B)]
+        res = pipe.roundtrip_many([(xh, (qch, qfh)) for xh, qch, qfh in ins], host_io=True)
+        h2d = sum(xh.numel() * 4 + qch.numel() * 4 + qfh.numel() * 4 for xh, qch, qfh in ins) \
+            + sum(c.numel() * 4 for _, _, c in res)
+        d2h = sum(o.numel() * 4 + c.numel() * 4 for o, _, c in res)
+        return h2d, d2h
 
     # ---- device-resident timing (value)
     dev_inputs = []
-    for s in range(total):
+    for s in range(total * B):
         xh, qch, qfh = host_inputs(s)
         if world > 1 or s == 0:
             dev_inputs.append((xh.to(dev), (qch.to(dev), qfh.to(dev))))
         else:
             dev_inputs.append(dev_inputs[0])
     for s in range(args.warmup):
-        step_device(*dev_inputs[s])
+        step_device(s)
     import gc
     gc.collect()
     gc.disable()  # no collector pauses inside the timed regions (re-enabled after the e2e loop)
@@ -295,10 +338,9 @@ def run_ours(args, rank, world, local_rank):
     step_wall = []
     for s in range(args.warmup, total):
         tw = time.perf_counter()
-        out = step_device(*dev_inputs[s])
-        npts += out.shape[0]
+        npts += step_device(s)
         step_wall.append(round((time.perf_counter() - tw) * 1e3, 2))
-    ev1.record()
+    ev1.record()  # the pipeline made this stream wait for every frame's stream
     barrier()
     t_dev = ev0.elapsed_time(ev1) * 1e-3
     launches = ops.launches() - l0
@@ -307,7 +349,7 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- end-to-end timing through the public API with host buffers (e2e)
     for s in range(min(args.warmup, 1)):
-        step_e2e(*host_inputs(s))
+        step_e2e(s)
     barrier()
     cc.reset_coder_stats()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -316,20 +358,29 @@ def run_ours(args, rank, world, local_rank):
     h2d = d2h = 0
     step_wall_e2e = []
     for s in range(args.warmup, total):
-        xh, qch, qfh = host_inputs(s)
         tw = time.perf_counter()
-        out, c_host = step_e2e(xh, qch, qfh)
+        a, b = step_e2e(s)
         step_wall_e2e.append(round((time.perf_counter() - tw) * 1e3, 2))
-        h2d += xh.numel() * 4 + qch.numel() * 4 + qfh.numel() * 4 + c_host.numel() * 4
-        d2h += out.numel() * 4 + c_host.numel() * 4
+        h2d += a
+        d2h += b
     e1.record()
     barrier()
     t_e2e = max(e0.elapsed_time(e1) * 1e-3, time.perf_counter() - t0)
-    gc.enable()
     h2d += cc.coder_stats["h2d_bytes"]
     d2h += cc.coder_stats["d2h_bytes"]
 
     # ---- max over ranks
+    # one frame at a time (no pipelining): the codec's latency, for reference
+    lat = []
+    for _ in range(2):
+        torch.cuda.synchronize()
+        tw = time.perf_counter()
+        s_, sh_, k_, c_ = model.compress(*dev_inputs[0])
+        model.decompress(coordinates=c_, strings=s_, shape=sh_, k=k_)
+        torch.cuda.synchronize()
+        lat.append(round((time.perf_counter() - tw) * 1e3, 2))
+    gc.enable()
+    pipe.close()
     (t_dev, t_e2e), npts_all = pcc_b200.frames.reduce_throughput([t_dev, t_e2e], npts, dev)
     if rank != 0:
         return
@@ -337,6 +388,9 @@ def run_ours(args, rank, world, local_rank):
     roof = None
     if not args.no_roofline:
         roof, _ = roofline_pass(model, *dev_inputs[0], peaks, clocks, args.dump_layers)
+    tf32 = None
+    if world == 1 and args.mode == "exact" and not args.no_tf32_pass:
+        tf32 = tf32_pass(args, model, dev, dev_inputs[0], B, peaks, clocks)
     base = None
     if world == 1 and not args.no_cpu_baseline:
         base = cpu_baseline(args, args.config)
@@ -347,28 +401,33 @@ def run_ours(args, rank, world, local_rank):
         "warmup": args.warmup, "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32" if args.mode == "exact" else "tf32",
         "data": "synthetic",
-        "config": {"workload": f"Ours.yaml random-init ({args.config}), encode+decode of one synthetic 10-bit "
+        "config": {"workload": f"Ours.yaml random-init ({args.config}), encode+decode of {B} x one synthetic 10-bit "
                                f"voxelised shell frame, radius {args.radius:g} -> {n_frame} points, RGB, "
                                f"uniform q=({args.q[0]:g},{args.q[1]:g}); in-memory variant (path=None)",
-                   "mode": args.mode, "frames_per_step_per_gpu": 1, "parallelism": f"frame-parallel x{world}",
+                   "mode": args.mode, "frames_per_step_per_gpu": B, "frames_in_flight_per_gpu": min(args.depth, B),
+                   "parallelism": f"frame-parallel x{world}, {min(args.depth, B)}-deep frame pipeline per GPU "
+                                  "(CPU range coder of one frame overlaps the kernels of the others)",
                    "l2": "per-step working set (>1 GB of activations and kernel maps) exceeds the 126 MB L2; no flush",
                    "includes_cpu_range_coder": True},
         "e2e": {"value": npts_all / t_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d // args.steps,
                 "d2h_bytes_per_step": d2h // args.steps, "ms_per_step": t_e2e / args.steps * 1e3},
         "gpu_launches": launches,
         "clocks": clocks,
-        "coder": {"encode_ms_per_step": coder["encode_s"] / args.steps * 1e3,
-                  "decode_ms_per_step": coder["decode_s"] / args.steps * 1e3,
-                  "copies_ms_per_step": (coder["d2h_s"] + coder["h2d_s"]) / args.steps * 1e3,
-                  "symbols_per_step": coder["symbols"] // args.steps,
-                  "note": "reference's sequential CPU rANS, inside ms_per_step; value_excl_coder removes it"},
-        "value_excl_coder": npts_all / max(t_dev - coder["encode_s"] - coder["decode_s"], 1e-9),
+        "coder": {"encode_ms_per_frame": coder["encode_s"] / (args.steps * B) * 1e3,
+                  "decode_ms_per_frame": coder["decode_s"] / (args.steps * B) * 1e3,
+                  "copies_ms_per_frame": (coder["d2h_s"] + coder["h2d_s"]) / (args.steps * B) * 1e3,
+                  "symbols_per_frame": coder["symbols"] // (args.steps * B),
+                  "note": "reference's sequential CPU rANS (rank 0's frames), inside the timed region; with "
+                          "several frames in flight it overlaps other frames' kernels"},
+        "single_frame_latency_ms": lat,
         "step_host_ms": {"device_resident": step_wall, "e2e": step_wall_e2e,
                          "note": "host wall clock per step on rank 0 (launch side; the decoded cloud's "
                                  "D2H ends each e2e step)"},
     }
     if roof is not None:
         line["roofline"] = roof
+    if tf32 is not None:
+        line["tf32"] = tf32
     if base is not None:
         line["cpu_baseline"] = base
     print(json.dumps(line))

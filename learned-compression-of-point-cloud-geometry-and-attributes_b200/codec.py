@@ -18,7 +18,7 @@ import torch.nn as nn
 
 from . import ops
 from . import me as ME
-from .compressai_compat import CompressionModel, EntropyBottleneck, GaussianConditional
+from .compressai_compat import CompressionModel, EntropyBottleneck, GaussianConditional, Wait, drive
 from ._lib import PccError
 
 RELU, LEAKY, NONE = ops.ACT_RELU, ops.ACT_LEAKY, ops.ACT_NONE
@@ -435,7 +435,14 @@ class MeanScaleHyperprior_Map(CompressionModel):
         return ST(y_hat_f, y.m), Q_hat, (y_lik.unsqueeze(0), z_lik.unsqueeze(0))
 
     def compress(self, y):
-        """(:341-381).  y is canonical already, so sort_tensor (:346-347) is the identity."""
+        return drive(self.compress_gen(y))
+
+    def decompress(self, points, strings, shape):
+        return drive(self.decompress_gen(points, strings, shape))
+
+    def compress_gen(self, y):
+        """(:341-381).  y is canonical already, so sort_tensor (:346-347) is the identity.
+        Generator: yields compressai_compat.Wait objects where the CPU coder is involved."""
         with stage("enc.h_a"):
             z = self.run_h_a(y)
         shape = [z.m.n]
@@ -445,13 +452,16 @@ class MeanScaleHyperprior_Map(CompressionModel):
         z_hat = ST(z_hat_f, z.m)  # == decompress(compress(z)) (:352-353): the coder is lossless
         with stage("enc.h_s"):
             params = self.run_h_s(z_hat, at_map=y.m)
-        with stage("enc.y_coder"):
-            y_string, y_sym, y_idx = self.gaussian_conditional.compress_fused(y.F, params.F, None)
+        if STAGE_MS is not None:
+            with stage("enc.y_coder"):
+                y_string, y_sym, y_idx = self.gaussian_conditional.compress_fused(y.F, params.F, None)
+        else:
+            y_string, y_sym, y_idx = yield from self.gaussian_conditional.compress_fused_gen(y.F, params.F, None)
         self.last = {"z": z, "z_hat": z_hat, "params": params, "y_symbols": y_sym, "indexes": y_idx,
                      "z_symbols": z_sym}
         return [y.m, z.m], [[y_string], [z_string]], shape
 
-    def decompress(self, points, strings, shape):
+    def decompress_gen(self, points, strings, shape):
         """(:384-414).  points = [y map, z map], both canonical (sort_points, :389-390)."""
         y_map, z_map = points
         with stage("dec.z_coder"):
@@ -460,9 +470,13 @@ class MeanScaleHyperprior_Map(CompressionModel):
         with stage("dec.h_q+h_s"):
             Q_hat = self.run_h_q(z_hat)
             params = self.run_h_s(z_hat, at_map=y_map)
-        with stage("dec.y_coder"):
-            y_hat_f = self.gaussian_conditional.decompress_fused(strings[0][0], params.F, None, y_map.n,
-                                                                 params.F.shape[1] // 2)
+        if STAGE_MS is not None:
+            with stage("dec.y_coder"):
+                y_hat_f = self.gaussian_conditional.decompress_fused(strings[0][0], params.F, None, y_map.n,
+                                                                     params.F.shape[1] // 2)
+        else:
+            y_hat_f = yield from self.gaussian_conditional.decompress_fused_gen(
+                strings[0][0], params.F, None, y_map.n, params.F.shape[1] // 2)
         self.last = {"z_hat": z_hat, "params": params}
         return ST(y_hat_f, y_map), Q_hat
 
@@ -549,16 +563,25 @@ class ColorModel(CompressionModel):
 
     @torch.no_grad()
     def compress(self, x, Q, path=None):
-        """model/model.py:95-147, in-memory variant: returns (strings, shape, k, coordinates)."""
+        """model/model.py:95-147: returns (strings, shape, k, coordinates), or writes `path`."""
+        return drive(self.compress_gen(x, Q, path))
+
+    @torch.no_grad()
+    def decompress(self, path=None, coordinates=None, strings=None, shape=None, k=None):
+        """model/model.py:152-208 -> [N, 6] float (xyz, rgb quantised to 8 bit)."""
+        return drive(self.decompress_gen(path, coordinates, strings, shape, k))
+
+    def compress_gen(self, x, Q, path=None):
+        """Generator form of compress (yields compressai_compat.Wait objects at the coder)."""
         with stage("enc.inputs"):
             inp, Qt = self._inputs(x, Q)
         with stage("enc.g_a"):
             y, Qy, k = self.g_a(inp, Qt)
         if self.entropy_model_map is None:
-            points, strings, shape = self.entropy_model.compress(y)
+            points, strings, shape = yield from self.entropy_model.compress_gen(y)
         else:
-            points, y_strings, y_shape = self.entropy_model.compress(y)
-            _, Q_strings, Q_shape = self.entropy_model_map.compress(Qy)
+            points, y_strings, y_shape = yield from self.entropy_model.compress_gen(y)
+            _, Q_strings, Q_shape = yield from self.entropy_model_map.compress_gen(Qy)
             strings, shape = [y_strings, Q_strings], [y_shape, Q_shape]
         self.last = {"y": y, "Q": Qy}
         coordinates = y.m.coords
@@ -568,9 +591,8 @@ class ColorModel(CompressionModel):
             return None
         return strings, shape, k, coordinates
 
-    @torch.no_grad()
-    def decompress(self, path=None, coordinates=None, strings=None, shape=None, k=None):
-        """model/model.py:152-208 -> [N, 6] float (xyz, rgb quantised to 8 bit)."""
+    def decompress_gen(self, path=None, coordinates=None, strings=None, shape=None, k=None):
+        """Generator form of decompress."""
         dev = self.device
         if path:
             from .bitstream import load_bitstream
@@ -585,10 +607,10 @@ class ColorModel(CompressionModel):
             y_map, _ = ops.canonical_map(coordinates.int(), 8)
             z_map = y_map.stride2().stride2()  # g_s.down_conv twice, only .C is used (:188-191)
         if self.entropy_model_map is None:
-            y_hat, Q_hat = self.entropy_model.decompress([y_map, z_map], strings, shape)
+            y_hat, Q_hat = yield from self.entropy_model.decompress_gen([y_map, z_map], strings, shape)
         else:
-            y_hat, _ = self.entropy_model.decompress([y_map, z_map], strings[0], shape[0])
-            Q_hat, _ = self.entropy_model_map.decompress([y_map, z_map], strings[1], shape[1])
+            y_hat, _ = yield from self.entropy_model.decompress_gen([y_map, z_map], strings[0], shape[0])
+            Q_hat, _ = yield from self.entropy_model_map.decompress_gen([y_map, z_map], strings[1], shape[1])
         self.last = {"y_hat": y_hat, "Q_hat": Q_hat}
         x_hat = self.g_s(y_hat, Q_hat, k=k)
         self.last["x_hat"] = x_hat

@@ -45,6 +45,90 @@ class LowerBound(nn.Module):
         return torch.max(x, self.bound.to(x.device))
 
 
+# ------------------------------------------------------------------------------ asynchronous coder
+# The range coder is the reference's sequential CPU algorithm; it runs in a small thread pool (the
+# ctypes call releases the GIL) so that a scheduler (pipeline.FramePipeline) can keep other frames'
+# kernels flowing while one frame is being coded.  Code that needs the coder is written as a
+# generator yielding `Wait` objects; `drive()` runs such a generator synchronously.
+import concurrent.futures as _cf
+
+_coder_pool = _cf.ThreadPoolExecutor(max_workers=4, thread_name_prefix="pcc-coder")
+
+
+class Wait:
+    """What a codec generator is waiting for: a CUDA event (device work / copy) or a coder future."""
+    __slots__ = ("event", "future")
+
+    def __init__(self, event=None, future=None):
+        self.event, self.future = event, future
+
+    def ready(self):
+        if self.event is not None and not self.event.query():
+            return False
+        return self.future is None or self.future.done()
+
+    def block(self):
+        if self.event is not None:
+            self.event.synchronize()
+        if self.future is not None:
+            self.future.result()
+
+
+def drive(gen):
+    """Run a codec generator to completion, blocking at every wait point."""
+    try:
+        w = next(gen)
+        while True:
+            w.block()
+            w = gen.send(None)
+    except StopIteration as e:
+        return e.value
+
+
+_pinned_free = {}
+
+
+def _pinned(shape, dtype):
+    """Page-locked host tensor from a free-list (cudaHostAlloc is far too slow for the hot path)."""
+    key = (tuple(shape), dtype)
+    lst = _pinned_free.get(key)
+    if lst:
+        t, ev = lst.pop()
+        if ev is not None:
+            ev.synchronize()
+        return t
+    return torch.empty(shape, dtype=dtype, pin_memory=True)
+
+
+def _pinned_release(t, after_event=None):
+    _pinned_free.setdefault((tuple(t.shape), t.dtype), []).append((t, after_event))
+
+
+def _d2h_async(*tensors):
+    """Device tensors -> pinned host tensors (async on the current stream) + the event to wait on."""
+    outs = []
+    for t in tensors:
+        h = _pinned(t.shape, t.dtype)
+        h.copy_(t, non_blocking=True)
+        coder_stats["d2h_bytes"] += h.numel() * h.element_size()
+        outs.append(h)
+    ev = torch.cuda.Event()
+    ev.record()
+    return outs, ev
+
+
+def _h2d_async(a, device):
+    """numpy array -> device tensor through a pinned staging buffer (async on the current stream)."""
+    h = _pinned(a.shape, torch.from_numpy(a).dtype)
+    h.numpy()[...] = a
+    t = h.to(device, non_blocking=True)
+    ev = torch.cuda.Event()
+    ev.record()
+    _pinned_release(h, ev)
+    coder_stats["h2d_bytes"] += a.nbytes
+    return t
+
+
 def _rows_cn(x):
     """[1, C, N] (typically ``F.t().unsqueeze(0)``) -> contiguous row-major [N, C] without a copy
     when the input is a transposed view."""
@@ -101,6 +185,15 @@ class EntropyModel(nn.Module):
                                  self._cdf_length.cpu().numpy().astype(np.int32),
                                  self._offset.cpu().numpy().astype(np.int32))
         return self._host_tables
+
+    def _encode_host(self, sym, idx):
+        """numpy symbols/indexes -> bytes (runs in a coder thread)."""
+        cdf, length, offset = self._tables()
+        t0 = time.perf_counter()
+        s = ops.rans_encode(sym, idx, cdf, length, offset)
+        coder_stats["encode_s"] += time.perf_counter() - t0
+        coder_stats["symbols"] += sym.size
+        return s
 
     def _encode(self, symbols_dev, indexes_dev):
         sym, idx = _to_host(symbols_dev), _to_host(indexes_dev)
@@ -296,10 +389,22 @@ class GaussianConditional(EntropyModel):
         sym, _ = ops.gc_quantize_index(y, torch.cat([m, m], dim=1), None, self._table_dev(y.device), self._scale_bound)
         return [self._encode(sym, indexes[0].contiguous())]
 
-    def compress_fused(self, y, params, rows):
-        """Fused path: y [N, C], params [Np, 2C] (scales | means), rows [N] -> bytes."""
+    def compress_fused_gen(self, y, params, rows):
+        """Fused path: y [N, C], params [Np, 2C] (scales | means), rows [N] -> (bytes, symbols, indexes).
+        Generator: yields Wait objects (symbols reaching the host, the coder finishing)."""
+        self._tables()  # materialise the host tables on the calling thread
         sym, idx = ops.gc_quantize_index(y, params, rows, self._table_dev(y.device), self._scale_bound)
-        return self._encode(sym, idx), sym, idx
+        (sym_h, idx_h), ev = _d2h_async(sym, idx)
+        yield Wait(event=ev)
+        fut = _coder_pool.submit(self._encode_host, sym_h.numpy(), idx_h.numpy())
+        yield Wait(future=fut)
+        string = fut.result()
+        _pinned_release(sym_h)
+        _pinned_release(idx_h)
+        return string, sym, idx
+
+    def compress_fused(self, y, params, rows):
+        return drive(self.compress_fused_gen(y, params, rows))
 
     def decompress(self, strings, indexes, dtype=torch.float, means=None):
         idx_dev = indexes[0].contiguous()
@@ -310,11 +415,20 @@ class GaussianConditional(EntropyModel):
         y_hat = ops.gc_dequantize(sym_dev, torch.cat([m, m], dim=1), None)
         return y_hat.t().unsqueeze(0)
 
-    def decompress_fused(self, string, params, rows, n, c):
-        """Fused path -> y_hat [N, C]."""
+    def decompress_fused_gen(self, string, params, rows, n, c):
+        """Fused path -> y_hat [N, C].  Generator (see compress_fused_gen)."""
+        self._tables()
         idx = ops.gc_build_indexes(params, rows, n, c, self._table_dev(params.device), self._scale_bound)
-        sym = self._decode(string, _to_host(idx)).reshape(c, n)
-        return ops.gc_dequantize(_to_dev(sym, params.device), params, rows)
+        (idx_h,), ev = _d2h_async(idx)
+        yield Wait(event=ev)
+        fut = _coder_pool.submit(self._decode, string, idx_h.numpy())
+        yield Wait(future=fut)
+        sym = fut.result().reshape(c, n)
+        _pinned_release(idx_h)
+        return ops.gc_dequantize(_h2d_async(sym, params.device), params, rows)
+
+    def decompress_fused(self, string, params, rows, n, c):
+        return drive(self.decompress_fused_gen(string, params, rows, n, c))
 
 
 class CompressionModel(nn.Module):

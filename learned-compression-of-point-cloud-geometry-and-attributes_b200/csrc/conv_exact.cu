@@ -306,8 +306,10 @@ template <int TN, bool VEC, int F2>
 static int launch_exact_v(const ConvParams& p, cudaStream_t st) {
   const size_t smem = sizeof(ExactSmem<TN>);
   dim3 grid((unsigned)ceil_div(p.n_out, CE_TM), (unsigned)ceil_div(p.cout, TN));
-  PCC_CHECK_CUDA(cudaFuncSetAttribute(conv_exact_kernel<TN, VEC, F2>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // once per instantiation and process (thread-safe static init): keeps driver calls off the launch path
+  static const cudaError_t attr = cudaFuncSetAttribute(conv_exact_kernel<TN, VEC, F2>,
+                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  PCC_CHECK_CUDA(attr);
   conv_exact_kernel<TN, VEC, F2><<<grid, CE_THREADS, smem, st>>>(p);
   PCC_CHECK_LAUNCH("conv_exact_kernel");
   return PCC_OK;

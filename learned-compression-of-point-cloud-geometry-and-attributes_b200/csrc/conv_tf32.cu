@@ -415,7 +415,9 @@ static int launch_tc(const TcParams& p, cudaStream_t st) {
   const int rc = make_map_2d(&tm_b, p.weight_t, (int64_t)p.K * p.cout, p.cin, BN);
   if (rc) return rc;
   const size_t smem = TcSmem<BN>::TOTAL;
-  PCC_CHECK_CUDA(cudaFuncSetAttribute(conv_tf32_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  static const cudaError_t attr =
+      cudaFuncSetAttribute(conv_tf32_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  PCC_CHECK_CUDA(attr);
   dim3 grid((unsigned)ceil_div(p.n_out, TC_TM), (unsigned)ceil_div(p.cout, BN));
   conv_tf32_kernel<BN><<<grid, TC_THREADS, smem, st>>>(tm_b, p);
   PCC_CHECK_LAUNCH("conv_tf32_kernel");
@@ -621,7 +623,9 @@ static int launch_tma(const TcParams& p, int64_t n_in, cudaStream_t st) {
   rc = make_map_2d(&tm_b, p.weight_t, (int64_t)p.K * p.cout, p.cin, BN);
   if (rc) return rc;
   const size_t smem = TmSmem<BN>::TOTAL;
-  PCC_CHECK_CUDA(cudaFuncSetAttribute(conv_tma_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  static const cudaError_t attr =
+      cudaFuncSetAttribute(conv_tma_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  PCC_CHECK_CUDA(attr);
   dim3 grid((unsigned)ceil_div(p.n_out, TC_TM), (unsigned)ceil_div(p.cout, BN));
   conv_tma_kernel<BN><<<grid, TM_THREADS, smem, st>>>(tm_a, tm_b, p);
   PCC_CHECK_LAUNCH("conv_tma_kernel");

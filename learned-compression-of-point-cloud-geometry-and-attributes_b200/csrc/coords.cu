@@ -372,6 +372,17 @@ static size_t unique_ws_bytes(int64_t m) {
          align_up(cub_sort_keys_bytes(m), 256) + 256;
 }
 
+// Page-locked per-thread staging for the counts a function hands back to the host: a D2H copy into
+// pageable memory is staged by the driver, into pinned memory it is a plain DMA + one stream sync.
+static int32_t* pinned_counts() {
+  static thread_local int32_t* p = [] {
+    int32_t* q = nullptr;
+    if (cudaHostAlloc(reinterpret_cast<void**>(&q), 64, cudaHostAllocDefault) != cudaSuccess) q = nullptr;
+    return q;
+  }();
+  return p;
+}
+
 // sorts raw[m] and writes the unique keys to out_keys; returns count through the host pointer
 static int sort_unique(uint64_t* raw, int64_t m, uint64_t* out_keys, int64_t* n_out, char* ws,
                        size_t ws_bytes, cudaStream_t st) {
@@ -395,10 +406,11 @@ static int sort_unique(uint64_t* raw, int64_t m, uint64_t* out_keys, int64_t* n_
   if (rc) return rc;
   compact_heads_kernel<<<grid_for(m), THREADS, 0, st>>>(sorted, m, flags, out_keys);
   PCC_CHECK_LAUNCH("compact_heads_kernel");
-  int32_t h = 0;
-  PCC_CHECK_CUDA(cudaMemcpyAsync(&h, total, 4, cudaMemcpyDeviceToHost, st));
+  int32_t hbuf = 0;
+  int32_t* h = pinned_counts() ? pinned_counts() : &hbuf;
+  PCC_CHECK_CUDA(cudaMemcpyAsync(h, total, 4, cudaMemcpyDeviceToHost, st));
   PCC_CHECK_CUDA(cudaStreamSynchronize(st));
-  *n_out = h;
+  *n_out = h[0];
   return PCC_OK;
 }
 
@@ -457,7 +469,8 @@ int pcc_coords_expand(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, 
   if (rc) return rc;
   expand_emit_kernel<<<grid_for(n), THREADS, 0, st>>>(keys, n, kernel_size, ts_in / 2, own, pos, raw, status);
   PCC_CHECK_LAUNCH("expand_emit_kernel");
-  int32_t h[2] = {0, 0};
+  int32_t hbuf[2] = {0, 0};
+  int32_t* h = pinned_counts() ? pinned_counts() : hbuf;
   PCC_CHECK_CUDA(cudaMemcpyAsync(h, total, 8, cudaMemcpyDeviceToHost, st));
   PCC_CHECK_CUDA(cudaStreamSynchronize(st));
   if (h[1]) {

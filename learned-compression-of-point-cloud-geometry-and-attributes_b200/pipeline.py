@@ -1,0 +1,92 @@
+"""Frame pipeline: several frames in flight on one GPU, scheduled cooperatively from ONE thread.
+
+One frame's encode+decode is a dependency chain with two long CPU-only links — the reference's
+sequential rANS coder (model/entropy_models.py:372,408; ~2.3 M symbols per direction at 800 k
+points) — during which the GPU has nothing to do for that frame.  Frames are independent
+(evaluate.py:95-110 codes them one at a time), so a sequence (BASELINE.json configs[3]) is coded with
+`depth` frames in flight: each frame is a generator (ColorModel.compress_gen / .decompress_gen) on
+its own CUDA stream that yields where it waits for a device->host copy or for the coder (which runs
+in compressai_compat's coder threads, GIL released).  The scheduler resumes whichever frame is
+ready, oldest first, so while one frame sits in the coder the other frames' kernels keep the SMs
+busy.  A single Python thread issues all launches: no GIL hand-offs between launch threads.
+No frame's result depends on the interleaving: every kernel of a frame is enqueued on that frame's
+stream in program order.
+"""
+import time
+from collections import deque
+
+import torch
+
+from .compressai_compat import Wait, _pinned, _pinned_release
+
+
+class _Frame:
+    __slots__ = ("index", "gen", "stream", "wait", "started")
+
+    def __init__(self, index, gen, stream):
+        self.index, self.gen, self.stream, self.wait, self.started = index, gen, stream, None, False
+
+
+class FramePipeline:
+    def __init__(self, model, depth=3, device=None):
+        self.model = model
+        self.depth = max(1, int(depth))
+        self.device = torch.device(device) if device is not None else model.device
+        self._streams = [torch.cuda.Stream(device=self.device) for _ in range(self.depth)]
+
+    def _roundtrip_gen(self, x, Q, host_io):
+        m = self.model
+        strings, shape, k, coords = yield from m.compress_gen(x, Q)
+        if host_io:
+            coords = coords.cpu()  # the latent coordinates leave the device with the strings
+        out = yield from m.decompress_gen(None, coords, strings, shape, k)
+        if host_io:
+            h = _pinned(out.shape, out.dtype)
+            h.copy_(out, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+            yield Wait(event=ev)
+            out = h.clone()
+            _pinned_release(h)
+        return out, strings, coords
+
+    @torch.no_grad()
+    def roundtrip_many(self, frames, host_io=False):
+        """frames: list of (x, Q) -> list of (decoded cloud, strings, latent coordinates), in order.
+        Inputs may live on the host (H2D happens on the frame's stream) or on the device; with
+        host_io the latent coordinates and the decoded cloud are returned in host memory."""
+        cur = torch.cuda.current_stream(self.device)
+        ready = torch.cuda.Event()
+        ready.record(cur)
+        pending = deque(enumerate(frames))
+        free = list(self._streams)
+        active, results = [], [None] * len(frames)
+        while pending or active:
+            while pending and free:
+                i, (x, Q) = pending.popleft()
+                s = free.pop()
+                s.wait_event(ready)
+                active.append(_Frame(i, self._roundtrip_gen(x, Q, host_io), s))
+            progressed = False
+            for f in list(active):
+                if f.started and not f.wait.ready():
+                    continue
+                progressed = True
+                with torch.cuda.stream(f.stream):
+                    try:
+                        f.wait = f.gen.send(None)
+                        f.started = True
+                    except StopIteration as e:
+                        results[f.index] = e.value
+                        done = torch.cuda.Event()
+                        done.record(f.stream)
+                        cur.wait_event(done)  # the caller's stream sees this frame's results
+                        active.remove(f)
+                        free.append(f.stream)
+                break  # rescan from the oldest frame after every step
+            if not progressed:
+                time.sleep(5e-5)
+        return results
+
+    def close(self):
+        pass

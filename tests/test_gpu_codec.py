@@ -113,3 +113,35 @@ def test_me_surface_matches_fused_path(pcc):
     mask[::3] = True
     p = ME.MinkowskiPruning()(a, mask)
     assert torch.equal(p.F, a.F[mask]) and torch.equal(p.C, a.C[mask])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("host_io", [False, True])
+def test_frame_pipeline_matches_sequential(pcc, host_io):
+    """Several frames in flight (cooperative scheduler, coder threads) give byte-identical strings and
+    bit-identical clouds to coding the frames one at a time."""
+    dev = "cuda:0"
+    model = pcc.ColorModel(pcc.OURS_CONFIG)
+    pcc.init_synthetic(model, 0)
+    model.eval().to(dev)
+    model.update()
+    frames = []
+    for t, r in enumerate([14.0, 22.0, 17.0, 25.0, 12.0]):
+        x = pcc.synthetic.shell_frame(r, center=[64, 64, 64], grid=128, seed=t)
+        qc, qf = pcc.synthetic.uniform_q_map(x, 0.5, 0.5)
+        frames.append((x.pin_memory(), (qc.pin_memory(), qf.pin_memory())) if host_io
+                      else (x.to(dev), (qc.to(dev), qf.to(dev))))
+    seq = []
+    for x, Q in frames:
+        s, sh, k, c = model.compress(x, Q)
+        seq.append((model.decompress(coordinates=c, strings=s, shape=sh, k=k), s, c))
+    pipe = pcc.pipeline.FramePipeline(model, depth=3, device=dev)
+    for _ in range(2):
+        got = pipe.roundtrip_many(frames, host_io=host_io)
+        torch.cuda.synchronize()
+        assert len(got) == len(seq)
+        for (o1, s1, c1), (o0, s0, c0) in zip(got, seq):
+            assert s1[0][0] == s0[0][0] and s1[1][0] == s0[1][0]
+            assert torch.equal(c1.cpu(), c0.cpu())
+            assert torch.equal(o1.cpu().view(torch.int32), o0.cpu().view(torch.int32))
+            assert o1.is_cuda != host_io
