@@ -35,6 +35,7 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--mode", default=os.environ.get("PCC_BENCH_MODE", "exact"), choices=["exact", "tf32"])
     ap.add_argument("--radius", type=float, default=252.0, help="shell radius (252 -> 799,458 voxels)")
+    ap.add_argument("--grid", type=int, default=1024, help="voxel grid edge (1024 = 10 bit; 4096 = 12 bit, configs[4])")
     ap.add_argument("--cpu-radius", type=float, default=89.0, help="shell radius of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
@@ -112,15 +113,15 @@ def make_model(cfg_name, device=None):
     return model, cfg
 
 
-def frame_for(rank, step, world, radius):
+def frame_for(rank, step, world, radius, grid=1024):
     """Rank-sharded synthetic sequence: rank r codes frames r, r + world, ... (frame-parallel)."""
     import pcc_b200
     if world == 1:
-        return pcc_b200.synthetic.shell_frame(radius, seed=0)
+        return pcc_b200.synthetic.shell_frame(radius, grid=grid, seed=0)
     t = pcc_b200.frames.frames_of_rank((step + 1) * world, rank, world)[step]  # = step * world + rank
     import numpy as np
     r = radius + 4.0 * np.sin(2.0 * np.pi * t / 300.0)
-    return pcc_b200.synthetic.shell_frame(r, seed=t)
+    return pcc_b200.synthetic.shell_frame(r, grid=grid, seed=t)
 
 
 # ------------------------------------------------------------------------------ reference arm
@@ -282,7 +283,7 @@ def run_ours(args, rank, world, local_rank):
     B = max(1, args.frames_per_step)
     # world == 1: the configs[1] frame, B copies per step; world > 1: rank r codes frames r, r + W, ...
     # of the synthetic sequence (configs[3]), B distinct frames per step
-    frames = [frame_for(rank, s, world, args.radius) for s in range(total * B if world > 1 else 1)]
+    frames = [frame_for(rank, s, world, args.radius, args.grid) for s in range(total * B if world > 1 else 1)]
     get = (lambda s: frames[s]) if world > 1 else (lambda s: frames[0])
     qmaps = {}
     pipe = pcc_b200.pipeline.FramePipeline(model, depth=min(args.depth, B), device=dev)
@@ -401,8 +402,8 @@ def run_ours(args, rank, world, local_rank):
         "warmup": args.warmup, "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32" if args.mode == "exact" else "tf32",
         "data": "synthetic",
-        "config": {"workload": f"Ours.yaml random-init ({args.config}), encode+decode of {B} x one synthetic 10-bit "
-                               f"voxelised shell frame, radius {args.radius:g} -> {n_frame} points, RGB, "
+        "config": {"workload": f"Ours.yaml random-init ({args.config}), encode+decode of {B} x one synthetic {(args.grid - 1).bit_length()}-bit "
+                               f"voxelised shell frame, radius {args.radius:g} in a {args.grid}^3 grid -> {n_frame} points, RGB, "
                                f"uniform q=({args.q[0]:g},{args.q[1]:g}); in-memory variant (path=None)",
                    "mode": args.mode, "frames_per_step_per_gpu": B, "frames_in_flight_per_gpu": min(args.depth, B),
                    "parallelism": f"frame-parallel x{world}, {min(args.depth, B)}-deep frame pipeline per GPU "

@@ -358,7 +358,12 @@ class SparseSynthesisTransform(nn.Module):
         predictions = []
         for s in (1, 2, 3):
             with stage(f"g_s.stage{s}.q_predict+scale"):
-                beta_gamma = seq5(Q, getattr(self, f"q_predict_{s}"))
+                # (beta, gamma) is read only at x's coordinates (model/blocks.py:37), so the last
+                # q_predict convolution is evaluated there; at stage 1 Q still lives on h_q's dilated
+                # map (132 k voxels for 18 k of x), afterwards Q and x share the map
+                qp = getattr(self, f"q_predict_{s}")
+                t = apply_conv(apply_conv(Q, qp[0], act=RELU), qp[2], act=RELU)
+                beta_gamma = apply_conv(t, qp[4], out_map=x.m)
                 x = getattr(self, f"scale_{s}")(x, beta_gamma)
             with stage(f"g_s.stage{s}.up"):
                 x, pred, up_map = getattr(self, f"up_{s}")(x, k=k[s - 1], full_predictions=full_predictions)
