@@ -225,21 +225,28 @@ def tf32_pass(args, model, dev, frame_dev, B, peaks, clocks):
     ops.set_default_mode(ops.MODE_TF32)
     try:
         pipe = pcc_b200.pipeline.FramePipeline(model, depth=min(args.depth, B), device=dev)
-        steps, warm = 3, 2
+        import gc
+        steps, warm = 3, 3
         for _ in range(warm):
             pipe.roundtrip_many([frame_dev] * B)
         torch.cuda.synchronize()
+        gc.collect()
+        gc.disable()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
         npts = 0
+        wall = []
         for _ in range(steps):
+            tw = time.perf_counter()
             npts += sum(o.shape[0] for o, _, _ in pipe.roundtrip_many([frame_dev] * B))
+            wall.append(round((time.perf_counter() - tw) * 1e3, 2))
         ev1.record()
         torch.cuda.synchronize()
+        gc.enable()
         t = ev0.elapsed_time(ev1) * 1e-3
         roof, _ = roofline_pass(model, *frame_dev, peaks, clocks, None)
         return {"value": npts / t, "unit": UNIT, "ms_per_frame": t / (steps * B) * 1e3, "steps": steps,
-                "warmup": warm, "dtype": "tf32", "roofline": roof,
+                "warmup": warm, "dtype": "tf32", "roofline": roof, "step_host_ms": wall,
                 "note": "tcgen05.mma kind::tf32 path, same frames and pipeline; tolerance mode, not bit-exact"}
     finally:
         ops.set_default_mode(ops.MODE_EXACT)

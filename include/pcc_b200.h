@@ -209,6 +209,25 @@ int pcc_eb_likelihood(const float* z, const float* medians, const float* eb_para
 int pcc_color_finalize(const uint64_t* keys, const float* feats, int64_t n, int32_t c, float* out,
                        void* stream);
 
+/* ------------------------------------------------------------------ coordinate side channel
+ * Replaces ColorModel.gpcc_encode / gpcc_decode (model/model.py:318-358, 360-395): the reference
+ * writes the stride-8 latent coordinates to an ASCII PLY, runs the G-PCC `tmc3` binary as a
+ * subprocess (lossless geometry, positionQuantizationScale = 1) and reads the file back.  tmc3 is
+ * an un-vendored dependency, so the stream here is this library's own lossless code, NOT G-PCC
+ * compatible: breadth-first octree over (x, y, z) / stride, Morton child order, one occupancy byte
+ * per internal node, `depth` levels (2^depth = side of the cube in stride units), no header.
+ * keys [dev]: unique packed keys of batch 0, coordinates >= 0 and multiples of `stride`.
+ * out [dev, 4-byte aligned, capacity >= n * depth rounded up to 4]; *nbytes [host] = stream length.
+ * Decoding writes the keys in Morton order (callers re-sort with pcc_sort_keys, as the reference
+ * re-sorts what tmc3 returns, model/model.py:262-264); cap = capacity of keys_out, *n_out [host].
+ * Both synchronise the stream.  ws: pcc_octree_ws_bytes(n) (encode) / (cap) (decode). */
+size_t pcc_octree_ws_bytes(int64_t n);
+int pcc_octree_encode(const uint64_t* keys, int64_t n, int32_t stride, int32_t depth, uint8_t* out,
+                      int64_t out_cap, int64_t* nbytes, void* ws, size_t ws_bytes, void* stream);
+int pcc_octree_decode(const uint8_t* bytes, int64_t nbytes, int32_t stride, int32_t depth,
+                      uint64_t* keys_out, int64_t cap, int64_t* n_out, void* ws, size_t ws_bytes,
+                      void* stream);
+
 /* ------------------------------------------------------------------ entropy coder (host)
  * CompressAI cpp_exts/rans/rans_interface.cpp + ryg_rans rans64.h and cpp_exts/ops/ops.cpp,
  * reached through EntropyBottleneck/GaussianConditional .compress/.decompress/.update

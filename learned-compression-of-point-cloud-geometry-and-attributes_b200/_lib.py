@@ -64,6 +64,9 @@ SIGNATURES = {
     "pcc_eb_dequantize": (I32, [P, P, I64, I32, P, P]),
     "pcc_eb_likelihood": (I32, [P, P, P, I64, I32, F32, P, P, P]),
     "pcc_color_finalize": (I32, [P, P, I64, I32, P, P]),
+    "pcc_octree_ws_bytes": (SZ, [I64]),
+    "pcc_octree_encode": (I32, [P, I64, I32, I32, P, I64, P, P, SZ, P]),
+    "pcc_octree_decode": (I32, [P, I64, I32, I32, P, I64, P, P, SZ, P]),
     "pcc_rans_encode_with_indexes": (I64, [P, P, I64, P, I32, P, P, I32, P, I64]),
     "pcc_rans_decode_with_indexes": (I32, [P, I64, P, I64, P, I32, P, P, I32, P]),
     "pcc_pmf_to_quantized_cdf": (I32, [P, I32, I32, P]),

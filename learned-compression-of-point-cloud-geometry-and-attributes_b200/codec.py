@@ -576,6 +576,26 @@ class ColorModel(CompressionModel):
         """model/model.py:152-208 -> [N, 6] float (xyz, rgb quantised to 8 bit)."""
         return drive(self.decompress_gen(path, coordinates, strings, shape, k))
 
+    def save_bitstream(self, path, points, strings, shape, k):
+        """model/model.py:214-263."""
+        from .bitstream import save_bitstream
+        return save_bitstream(path, points, strings, shape, k)
+
+    def load_bitstream(self, path):
+        """model/model.py:267-315."""
+        from .bitstream import load_bitstream
+        return load_bitstream(path, self.device)
+
+    def gpcc_encode(self, points, directory=None):
+        """model/model.py:318-358 (own octree code instead of the tmc3 subprocess; `directory` unused)."""
+        from .bitstream import gpcc_encode
+        return gpcc_encode(points)
+
+    def gpcc_decode(self, bin, directory=None):
+        """model/model.py:360-395."""
+        from .bitstream import gpcc_decode
+        return gpcc_decode(bin, self.device)
+
     def compress_gen(self, x, Q, path=None):
         """Generator form of compress (yields compressai_compat.Wait objects at the coder)."""
         with stage("enc.inputs"):
@@ -601,7 +621,7 @@ class ColorModel(CompressionModel):
         dev = self.device
         if path:
             from .bitstream import load_bitstream
-            coordinates, strings, shape, k = load_bitstream(path)
+            coordinates, strings, shape, k = load_bitstream(path, dev)
         coordinates = coordinates.to(dev)
         if coordinates.shape[1] == 3:
             coordinates = torch.cat([torch.zeros((coordinates.shape[0], 1), device=dev,

@@ -531,6 +531,43 @@ def color_finalize(keys, feats):
     return out
 
 
+# ---------------------------------------------------------------------------- side channel
+def octree_encode(keys, stride, depth):
+    """Unique packed keys (batch 0, coordinates >= 0 on the `stride` grid) -> occupancy bytes."""
+    _need_cuda(keys, "keys")
+    n = keys.shape[0]
+    if n == 0:
+        return b""
+    cap = ((n * depth + 3) // 4) * 4
+    out = torch.empty(cap, dtype=torch.uint8, device=keys.device)
+    wsb = _L().pcc_octree_ws_bytes(n)
+    ws = _ws(wsb, keys.device)
+    nbytes = ctypes.c_int64(0)
+    check(_L().pcc_octree_encode(_ptr(keys), n, stride, depth, _ptr(out), cap, ctypes.byref(nbytes), _ptr(ws), wsb,
+                                 _stream()), "pcc_octree_encode")
+    _count(5)
+    return out[:nbytes.value].cpu().numpy().tobytes()
+
+
+def octree_decode(stream, stride, depth, device, cap=None):
+    """Occupancy bytes -> packed keys in Morton order (int64 tensor on `device`)."""
+    import numpy as np
+    nbytes = len(stream)
+    if nbytes == 0:
+        return torch.empty(0, dtype=torch.int64, device=device)
+    dev_bytes = torch.from_numpy(np.frombuffer(stream, dtype=np.uint8).copy()).to(device)
+    cap = int(cap) if cap else 8 * nbytes
+    keys = torch.empty(cap, dtype=torch.int64, device=device)
+    wsb = _L().pcc_octree_ws_bytes(cap)
+    ws = _ws(wsb, device)
+    n_out = ctypes.c_int64(0)
+    with torch.cuda.device(device):
+        check(_L().pcc_octree_decode(_ptr(dev_bytes), nbytes, stride, depth, _ptr(keys), cap, ctypes.byref(n_out),
+                                     _ptr(ws), wsb, _stream()), "pcc_octree_decode")
+    _count(2)
+    return keys[:n_out.value]
+
+
 # ---------------------------------------------------------------------------- host coder
 def _np_ptr(a):
     return ctypes.c_void_p(a.ctypes.data)
