@@ -343,11 +343,12 @@ def run_ours(args, rank, world, local_rank):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     npts = 0
-    step_wall = []
+    step_wall, pipe_stats = [], []
     for s in range(args.warmup, total):
         tw = time.perf_counter()
         npts += step_device(s)
         step_wall.append(round((time.perf_counter() - tw) * 1e3, 2))
+        pipe_stats.append({k: round(v, 1) for k, v in pipe.stats.items()})
     ev1.record()  # the pipeline made this stream wait for every frame's stream
     barrier()
     t_dev = ev0.elapsed_time(ev1) * 1e-3
@@ -428,7 +429,7 @@ def run_ours(args, rank, world, local_rank):
                   "note": "reference's sequential CPU rANS (rank 0's frames), inside the timed region; with "
                           "several frames in flight it overlaps other frames' kernels"},
         "single_frame_latency_ms": lat,
-        "step_host_ms": {"device_resident": step_wall, "e2e": step_wall_e2e,
+        "step_host_ms": {"device_resident": step_wall, "e2e": step_wall_e2e, "pipeline": pipe_stats,
                          "note": "host wall clock per step on rank 0 (launch side; the decoded cloud's "
                                  "D2H ends each e2e step)"},
     }

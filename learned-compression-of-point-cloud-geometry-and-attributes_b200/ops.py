@@ -4,6 +4,7 @@ torch is plumbing here (device memory, streams); every computation is a ``pcc_*`
 libpcc_b200.so.  There is no CPU fallback: tensors must live on a CUDA device.
 """
 import ctypes
+import weakref
 
 import torch
 
@@ -195,7 +196,7 @@ class CoordMap:
         transpose: targets q - d*ts_out, probed only when aligned to ts_in."""
         key = (id(out_map), kernel_size, transpose)
         km = self._kmaps.get(key)
-        if km is not None and km[0] is out_map:
+        if km is not None and km[0]() is out_map:
             return km[1]
         K = kernel_size ** 3
         n_out = out_map.n
@@ -218,7 +219,10 @@ class CoordMap:
                                       _ptr(ws), wsb, _stream()), "pcc_kernel_map")
             _count(1 if order is None else 7)
         kmap = KernelMap(nbr, tapmask, K, n_out, stride, order)
-        self._kmaps[key] = (out_map, kmap)
+        # weak reference: out_map is often this map itself (stride-1 layers) or a map that caches the
+        # transposed direction back to this one; a strong reference would make the pair collectable
+        # only by the cycle collector and keep its kernel maps (K x n_out x 4 bytes) alive until then
+        self._kmaps[key] = (weakref.ref(out_map), kmap)
         return kmap
 
 

@@ -33,6 +33,7 @@ class FramePipeline:
         self.depth = max(1, int(depth))
         self.device = torch.device(device) if device is not None else model.device
         self._streams = [torch.cuda.Stream(device=self.device) for _ in range(self.depth)]
+        self.stats = {}  # host-side accounting of the last roundtrip_many call
 
     def _roundtrip_gen(self, x, Q, host_io):
         m = self.model
@@ -61,6 +62,7 @@ class FramePipeline:
         pending = deque(enumerate(frames))
         free = list(self._streams)
         active, results = [], [None] * len(frames)
+        st = self.stats = {"resumes": 0, "resume_ms": 0.0, "max_resume_ms": 0.0, "idle_ms": 0.0}
         while pending or active:
             while pending and free:
                 i, (x, Q) = pending.popleft()
@@ -72,6 +74,7 @@ class FramePipeline:
                 if f.started and not f.wait.ready():
                     continue
                 progressed = True
+                t0 = time.perf_counter()
                 with torch.cuda.stream(f.stream):
                     try:
                         f.wait = f.gen.send(None)
@@ -83,9 +86,15 @@ class FramePipeline:
                         cur.wait_event(done)  # the caller's stream sees this frame's results
                         active.remove(f)
                         free.append(f.stream)
+                dt = (time.perf_counter() - t0) * 1e3
+                st["resumes"] += 1
+                st["resume_ms"] += dt
+                st["max_resume_ms"] = max(st["max_resume_ms"], dt)
                 break  # rescan from the oldest frame after every step
             if not progressed:
+                t0 = time.perf_counter()
                 time.sleep(5e-5)
+                st["idle_ms"] += (time.perf_counter() - t0) * 1e3
         return results
 
     def close(self):
