@@ -49,6 +49,31 @@ struct ConvParams {
   float slope;
 };
 
+// bias -> activation -> FiLM -> residual -> (tf32 rounding) -> store, one output element
+__device__ __forceinline__ void conv_epilogue(const ConvParams& p, int64_t o, int64_t frow, int64_t rrow, int col,
+                                              float v) {
+  if (p.bias) v = __fadd_rn(v, __ldg(p.bias + col));
+  if (p.act == PCC_ACT_RELU)
+    v = fmaxf(v, 0.0f);
+  else if (p.act == PCC_ACT_LEAKY)
+    v = v > 0.0f ? v : __fmul_rn(v, p.slope);
+  if (p.film_c) {
+    float beta = 0.0f, gamma = 0.0f;
+    if (frow >= 0) {
+      const int fc = p.film_c == 1 ? 0 : col;
+      beta = __ldg(p.film + frow * 2 * p.film_c + fc);
+      gamma = __ldg(p.film + frow * 2 * p.film_c + p.film_c + fc);
+    }
+    v = __fadd_rn(__fmul_rn(v, beta), gamma);
+  }
+  if (p.residual) {
+    const float r = rrow >= 0 ? __ldg(p.residual + rrow * p.cout + col) : 0.0f;
+    v = __fadd_rn(v, r);
+  }
+  if (p.flags & PCC_CONV_ROUND_OUT_TF32) v = round_tf32(v);
+  p.out[o * p.out_stride + col] = v;
+}
+
 template <int TN>
 struct ExactSmem {
   float a[CE_STAGES][CE_TM][CE_APITCH];
@@ -276,30 +301,135 @@ conv_exact_kernel(const ConvParams p) {
 #pragma unroll
     for (int c = 0; c < CN; ++c) {
       const int col = co_base + cbase + ((CN == 8) ? ((c >> 2) * 32 + (c & 3)) : c);
-      if (col >= p.cout) continue;
-      float v = acc[i][c];
-      if (p.bias) v = __fadd_rn(v, __ldg(p.bias + col));
-      if (p.act == PCC_ACT_RELU)
-        v = fmaxf(v, 0.0f);
-      else if (p.act == PCC_ACT_LEAKY)
-        v = v > 0.0f ? v : __fmul_rn(v, p.slope);
-      if (p.film_c) {
-        float beta = 0.0f, gamma = 0.0f;
-        if (frow >= 0) {
-          const int fc = p.film_c == 1 ? 0 : col;
-          beta = __ldg(p.film + frow * 2 * p.film_c + fc);
-          gamma = __ldg(p.film + frow * 2 * p.film_c + p.film_c + fc);
-        }
-        v = __fadd_rn(__fmul_rn(v, beta), gamma);
-      }
-      if (p.residual) {
-        const float r = rrow >= 0 ? __ldg(p.residual + rrow * p.cout + col) : 0.0f;
-        v = __fadd_rn(v, r);
-      }
-      if (p.flags & PCC_CONV_ROUND_OUT_TF32) v = round_tf32(v);
-      p.out[o * p.out_stride + col] = v;
+      if (col < p.cout) conv_epilogue(p, o, frow, rrow, col, acc[i][c]);
     }
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Narrow-output variant (cout <= 4: occupancy / quality / colour heads).  With so few output
+// channels the register-tile kernel above spends its time on padded columns; here one thread owns
+// one output row and all (<= 4) channels, so the arithmetic is negligible and the kernel runs at
+// the speed the gathered rows arrive (L2 -> shared memory, cp.async, CH_STAGES deep, 4 CTAs / SM).
+// Same summation order (k ascending, ci ascending, one FMA chain per output element).
+constexpr int CH_STAGES = 3;
+
+struct HeadSmem {
+  float a[CH_STAGES][CE_TM][CE_APITCH];
+  float b[CH_STAGES][CE_TK][4];
+};
+
+__global__ void __launch_bounds__(CE_THREADS, 4)
+conv_head_kernel(const ConvParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  HeadSmem& sm = *reinterpret_cast<HeadSmem*>(smem_raw);
+  const int tid = threadIdx.x;
+  const int64_t tile_base = (int64_t)blockIdx.x * CE_TM;
+  const int nchunks = (p.cin + CE_TK - 1) / CE_TK;
+  const uint32_t kfull = p.K >= 32 ? 0xffffffffu : ((1u << p.K) - 1u);
+  const uint32_t mask = p.tapmask ? (p.tapmask[blockIdx.x] & kfull) : kfull;
+  const int nsteps = __popc(mask) * nchunks;
+
+  uint32_t pmask = mask;
+  int pk = pmask ? (__ffs(pmask) - 1) : 0;
+  int pchunk = 0;
+  int idx[4], nidx[4];
+  auto load_idx = [&](int k, int (&dst)[4]) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t t = tile_base + (tid >> 3) + 32 * j;
+      dst[j] = (t < p.n_out) ? __ldg(p.nbr + (int64_t)k * p.nbr_stride + t) : -1;
+    }
+  };
+  {
+    load_idx(pk, idx);
+    const uint32_t rest = pmask & (pmask - 1);
+    if (rest) load_idx(__ffs(rest) - 1, nidx);
+  }
+
+  auto issue = [&](int stage) {
+    const int ci0 = pchunk * CE_TK;
+    const int q = tid & 7;
+    const int ci = ci0 + q * 4;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int r = (tid >> 3) + 32 * j;
+      const int ix = idx[j];
+      const bool ok = ix >= 0 && ci < p.cin;
+      cp_async16(&sm.a[stage][r][q * 4], ok ? p.in + (int64_t)ix * p.cin + ci : p.in, ok ? 16 : 0);
+    }
+    if (tid < CE_TK) {  // weight rows ci0 + tid of offset pk, padded to 4 columns
+      const int wc = ci0 + tid;
+      float w[4] = {0.f, 0.f, 0.f, 0.f};
+      if (wc < p.cin) {
+        const float* wr = p.weight + ((int64_t)pk * p.cin + wc) * p.cout;
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          if (c < p.cout) w[c] = __ldg(wr + c);
+      }
+      *reinterpret_cast<float4*>(&sm.b[stage][tid][0]) = make_float4(w[0], w[1], w[2], w[3]);
+    }
+    if (++pchunk == nchunks) {
+      pchunk = 0;
+      pmask &= pmask - 1;
+      pk = pmask ? (__ffs(pmask) - 1) : 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) idx[j] = nidx[j];
+      const uint32_t rest = pmask & (pmask - 1);
+      if (rest) load_idx(__ffs(rest) - 1, nidx);
+    }
+  };
+
+#pragma unroll
+  for (int s = 0; s < CH_STAGES - 1; ++s) {
+    if (s < nsteps) issue(s);
+    cp_async_commit();
+  }
+
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int s = 0; s < nsteps; ++s) {
+    cp_async_wait<CH_STAGES - 2>();
+    __syncthreads();
+    if (s + CH_STAGES - 1 < nsteps) issue((s + CH_STAGES - 1) % CH_STAGES);
+    cp_async_commit();
+    const int st = s % CH_STAGES;
+    if (tid < CE_TM) {
+#pragma unroll
+      for (int kv = 0; kv < CE_TK / 4; ++kv) {
+        const float4 a = *reinterpret_cast<const float4*>(&sm.a[st][tid][kv * 4]);
+        const float av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float4 w = *reinterpret_cast<const float4*>(&sm.b[st][kv * 4 + e][0]);
+          acc[0] = __fmaf_rn(av[e], w.x, acc[0]);
+          acc[1] = __fmaf_rn(av[e], w.y, acc[1]);
+          acc[2] = __fmaf_rn(av[e], w.z, acc[2]);
+          acc[3] = __fmaf_rn(av[e], w.w, acc[3]);
+        }
+      }
+    }
+  }
+  cp_async_wait<0>();
+
+  const int64_t t = tile_base + tid;
+  if (tid >= CE_TM || t >= p.n_out) return;
+  const int64_t o = p.order ? (int64_t)__ldg(p.order + t) : t;
+  int64_t frow = o, rrow = o;
+  if (p.film_c && p.film_rows) frow = __ldg(p.film_rows + o);
+  if (p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
+#pragma unroll
+  for (int c = 0; c < 4; ++c)
+    if (c < p.cout) conv_epilogue(p, o, frow, rrow, c, acc[c]);
+}
+
+static int launch_head(const ConvParams& p, cudaStream_t st) {
+  const size_t smem = sizeof(HeadSmem);
+  static const cudaError_t attr =
+      cudaFuncSetAttribute(conv_head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  PCC_CHECK_CUDA(attr);
+  conv_head_kernel<<<(unsigned)ceil_div(p.n_out, CE_TM), CE_THREADS, smem, st>>>(p);
+  PCC_CHECK_LAUNCH("conv_head_kernel");
+  return PCC_OK;
 }
 
 template <int TN, bool VEC, int F2>
@@ -339,6 +469,8 @@ int conv_exact(const pcc_conv_args* a, cudaStream_t st) {
   p.film = a->film; p.film_rows = a->film_rows; p.residual = a->residual; p.res_rows = a->res_rows;
   p.order = a->order; p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
   p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope; p.flags = a->flags;
+  if (a->cout <= 4 && a->cin % 4 == 0 && a->cin >= 16 && (reinterpret_cast<uintptr_t>(p.in) & 15) == 0)
+    return launch_head(p, st);
   // a grid that cannot fill 2 CTAs on every SM is split further along the output channels
   const int64_t tiles = ceil_div(p.n_out, CE_TM);
   const bool small_grid = tiles * ceil_div(p.cout, 128) < 2 * (int64_t)sm_count();

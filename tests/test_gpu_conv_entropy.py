@@ -57,13 +57,15 @@ def test_conv_variants_bitwise(pcc, oracle, ks, stride, transpose):
     assert np.array_equal(got.cpu().numpy().view(np.uint32), ref.F.view(np.uint32))
 
 
-@pytest.mark.parametrize("film_c", [0, 1, 48])
+@pytest.mark.parametrize("cin,cout,film_c", [(24, 48, 0), (24, 48, 1), (24, 48, 48),
+                                             (64, 4, 0), (64, 4, 1), (64, 4, 4), (128, 3, 3), (40, 2, 1), (16, 1, 1)])
 @pytest.mark.parametrize("act", [0, 1, 2])
-def test_conv_epilogue_bitwise(pcc, oracle, film_c, act):
-    """bias -> activation -> FiLM (x*beta+gamma, model/blocks.py:40) -> residual (model/blocks.py:50)."""
-    rng = np.random.default_rng(film_c + act)
+def test_conv_epilogue_bitwise(pcc, oracle, cin, cout, film_c, act):
+    """bias -> activation -> FiLM (x*beta+gamma, model/blocks.py:40) -> residual (model/blocks.py:50);
+    cout <= 4 with cin % 4 == 0 runs the narrow-output kernel (conv_head_kernel)."""
+    rng = np.random.default_rng(film_c + act + cin)
     m, keys, cs = _setup(pcc, oracle, 2500, 20, 1, 5)
-    n, cin, cout = m.n, 24, 48
+    n = m.n
     x = rng.standard_normal((n, cin)).astype(np.float32)
     W = (rng.standard_normal((27, cin, cout)) / 10).astype(np.float32)
     b = rng.standard_normal((1, cout)).astype(np.float32)
