@@ -205,6 +205,13 @@ def roofline_pass(model, x_dev, q_dev, peaks, clocks, dump=None):
             "launches": len(dom), "avg_launch_ms": t_ms / len(dom), "peak_source": src,
             "share_of_conv_time": t_ms / sum(r["ms"] for r in recs),
             "hbm_gbs_algorithmic": sum(conv_bytes(r) for r in dom) / (t_ms * 1e-3) / 1e9}
+    try:  # DRAM traffic of one captured launch (ncu --set full), committed under profiles/
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_traffic.json")) as f:
+            tr = json.load(f)["tf32" if tf32 else "exact"]
+        roof["traffic"] = tr["traffic_bytes"]
+        roof["traffic_detail"] = {k: tr[k] for k in ("launch", "algorithmic_bytes", "source")}
+    except (OSError, KeyError, ValueError):
+        pass
     if dump:
         with open(dump, "w") as f:
             f.write("cin,cout,K,n_in,n_out,pairs,mode,ms,tflops,alg_GBs\n")
