@@ -20,6 +20,7 @@ from . import ops
 from . import me as ME
 from .compressai_compat import CompressionModel, EntropyBottleneck, GaussianConditional, Wait, drive
 from ._lib import PccError
+from .slab import SlabMap
 
 RELU, LEAKY, NONE = ops.ACT_RELU, ops.ACT_LEAKY, ops.ACT_NONE
 
@@ -80,8 +81,17 @@ class ST:
 def apply_conv(x, layer, out_map=None, transpose=False, **epilogue):
     """One fused convolution: x (ST) -> ST on out_map (default: same map)."""
     out_map = x.m if out_map is None else out_map
+    if isinstance(x.m, SlabMap):  # one slab of a partitioned scene: owned rows computed, halo rows exchanged
+        return ST(x.m.conv(x.F, out_map, layer, transpose, epilogue), out_map)
     kmap = x.m.kernel_map(out_map, layer.kernel_size, transpose=transpose)
     return ST(ops.conv(x.F, kmap, layer.kernel, layer.bias, **epilogue), out_map)
+
+
+def on_map(m, F):
+    """Features of m's rows as a tensor over m: on a SlabMap, owned-row features get their halo rows."""
+    if isinstance(m, SlabMap) and F.shape[0] != m.n_local:
+        return m.lift(F)
+    return F
 
 
 def rows_of(src_map, dst_map):
@@ -197,6 +207,8 @@ class GenerativeUpBlock(nn.Module):
     @staticmethod
     def _topk(logits, cand_map, k):
         """_topk_prediction (:130-150): per batch id, the k largest logits of channel 0."""
+        if isinstance(cand_map, SlabMap):  # scene-wide k over all slabs
+            return cand_map.topk(logits, int(k[0]))
         nb = int((cand_map.keys[-1] >> 48).item()) + 1 if cand_map.n else 0
         if nb <= 1:
             return ops.topk_rows(logits, int(k[0]))
@@ -217,8 +229,11 @@ class GenerativeUpBlock(nn.Module):
         else:
             logits = self._logits(x, full_predictions)
         sel = self._topk(logits, cand, k)
-        up_map = ops.CoordMap(ops.take_keys(cand.keys, sel), cand.ts, True)  # predictions.C[mask] (:164)
-        x = ST(ops.gather_rows(x.F, sel), up_map)                              # _prune_coords (:101-128)
+        if isinstance(cand, SlabMap):
+            up_map = cand.select(sel)
+        else:
+            up_map = ops.CoordMap(ops.take_keys(cand.keys, sel), cand.ts, True)  # predictions.C[mask] (:164)
+        x = ST(on_map(up_map, ops.gather_rows(x.F, sel)), up_map)               # _prune_coords (:101-128)
         if not self.dense and self.condition_ablation is None:
             x = seq3(x, self.conv_2)
         return x, ST(logits, cand), up_map
@@ -266,6 +281,8 @@ class ConditionEncoder(nn.Module):
 
 def _count_per_batch(m):
     """AnalysisTransform.count_per_batch (model/transforms.py:65-71); maps are batch-sorted."""
+    if isinstance(m, SlabMap):
+        return [m.count_total()]
     if m.n == 0:
         return []
     nb = int((m.keys.max() >> 48).item()) + 1
@@ -301,7 +318,7 @@ class AnalysisTransform(nn.Module):
         if self.cond_conv is not None:
             Q_plus = seq3(x, self.cond_conv)
             # Q.F + Q_plus.features_at_coordinates(Q.C)  (:94-98)
-            Q = ST(ops.gather_rows(Q_plus.F, rows_of(x.m, Q.m), add=Q.F), Q.m)
+            Q = ST(on_map(Q.m, ops.gather_rows(Q_plus.F, rows_of(x.m, Q.m), add=Q.F)), Q.m)
         Q, beta_gammas = self.condition_encoder(Q)
         x = apply_conv(x, self.pre_conv[0], act=RELU)
         x = apply_conv(x, self.down_1, out_map=x.m.stride2())
@@ -313,7 +330,7 @@ class AnalysisTransform(nn.Module):
         x = apply_conv(x, self.down_3, out_map=x.m.stride2())
         x = self.scale_3(x, beta_gammas[2])
         x = apply_conv(x, self.post_conv)
-        Q = ST(ops.gather_rows(Q.F, rows_of(Q.m, x.m)), x.m)  # (:123-125)
+        Q = ST(on_map(x.m, ops.gather_rows(Q.F, rows_of(Q.m, x.m))), x.m)  # (:123-125)
         k.reverse()
         return x, Q, k
 
@@ -352,7 +369,7 @@ class SparseSynthesisTransform(nn.Module):
         with stage("g_s.pre"):
             if self.cond_conv is not None:
                 Q_plus = seq3(x, self.cond_conv)
-                Q = ST(ops.gather_rows(Q_plus.F, rows_of(x.m, Q.m), add=Q.F), Q.m)  # (:258-265)
+                Q = ST(on_map(Q.m, ops.gather_rows(Q_plus.F, rows_of(x.m, Q.m), add=Q.F)), Q.m)  # (:258-265)
             x = apply_conv(x, self.pre_conv[0], act=RELU)
             Q = seq5(Q, self.q_pre_conv)
         predictions = []
