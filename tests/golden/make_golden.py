@@ -25,17 +25,36 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, ROOT)
 REF = "/root/reference"
 
-CASES = [  # name, yaml, product config name, shell radius, seed, (q_g, q_a)
-    ("ours_r14", "configs/Ours.yaml", "OURS_CONFIG", 14.0, 0, (0.5, 0.5)),
-    ("ours_r11_q", "configs/Ours.yaml", "OURS_CONFIG", 11.0, 3, (0.2, 0.9)),
-    ("ablation_r12", "configs/Ablation_NoCondition_Convolution.yaml", "ABLATION_CONFIG", 12.0, 1, (0.75, 0.25)),
+CASES = [  # name, yaml, product config name, shell radius, seed, (q_g, q_a), non-uniform map or None
+    ("ours_r14", "configs/Ours.yaml", "OURS_CONFIG", 14.0, 0, (0.5, 0.5), None),
+    ("ours_r11_q", "configs/Ours.yaml", "OURS_CONFIG", 11.0, 3, (0.2, 0.9), None),
+    ("ablation_r12", "configs/Ablation_NoCondition_Convolution.yaml", "ABLATION_CONFIG", 12.0, 1, (0.75, 0.25), None),
+    # view-dependent gradient along y and region of interest beyond x = 64 (evaluate_view_dep.py:209-216,252-258)
+    ("ours_r13_view", "configs/Ours.yaml", "OURS_CONFIG", 13.0, 4, (0.8, 1.0), ("view", 1, 52.0, 76.0)),
+    ("ours_r12_roi", "configs/Ours.yaml", "OURS_CONFIG", 12.0, 5, (1.0, 0.6), ("roi", 0, 64.0)),
 ]
+
+
+def quality_features(x, q, kind):
+    """Per-point [q_g, q_a] the way the reference's scripts build them (numpy, float64 scores)."""
+    pts = x.numpy()[:, :3].astype(np.float64)
+    if kind is None:
+        return None
+    if kind[0] == "view":
+        _, axis, lo, hi = kind
+        scores = np.clip((pts[:, axis] - lo) / (hi - lo), 0, 1)
+    else:
+        _, axis, plane = kind
+        scores = np.where(pts[:, axis] < plane, 0, 1)
+    q_map_g = (q[0] * scores).reshape(-1, 1)
+    q_map_a = (q[1] * scores).reshape(-1, 1)
+    return torch.cat([torch.tensor(q_map_g), torch.tensor(q_map_a)], dim=1).type(torch.float32)  # utils.py:442
 
 
 def main():
     import pcc_b200
     from oracle import ref_shims
-    for name, yml, cfg_name, radius, seed, q in CASES:
+    for name, yml, cfg_name, radius, seed, q, kind in CASES:
         cfg = yaml.safe_load(open(os.path.join(REF, yml)))["model"]
         assert cfg == getattr(pcc_b200, cfg_name), f"{yml} differs from pcc_b200.{cfg_name}"
         ref_model = ref_shims.load_reference_model(cfg, REF)
@@ -50,6 +69,8 @@ def main():
         ref_model.update()
         x = pcc_b200.synthetic.shell_frame(radius, center=[64, 64, 64], grid=128, seed=seed)
         qc, qf = pcc_b200.synthetic.uniform_q_map(x, *q)
+        if kind is not None:
+            qf = quality_features(x, q, kind)
         import MinkowskiEngine as ME  # the stand-in
         with torch.no_grad():
             Q = ME.SparseTensor(coordinates=qc, features=qf)     # utils.py:436-445
@@ -65,7 +86,8 @@ def main():
         np.savez_compressed(
             os.path.join(HERE, name + ".npz"),
             config=cfg_name, radius=radius, seed=seed, q=np.array(q, np.float32),
-            x=x.numpy().astype(np.float32),
+            x=x.numpy().astype(np.float32), qf=qf.numpy().astype(np.float32),
+            qkind=np.array([] if kind is None else [{"view": 0.0, "roi": 1.0}[kind[0]]] + [float(v) for v in kind[1:]]),
             y_string=np.frombuffer(strings[0][0], np.uint8), z_string=np.frombuffer(strings[1][0], np.uint8),
             shape=np.array(shape, np.int64), k=np.array([int(kk[0]) for kk in k], np.int64),
             coordinates=coords, out=out.astype(np.float32))

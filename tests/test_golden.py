@@ -22,7 +22,22 @@ def _canon_out(out):
 
 
 def test_golden_fixtures_present():
-    assert len(GOLDEN) >= 3
+    assert len(GOLDEN) >= 5
+
+
+def _qmap(pcc, g, x):
+    """The fixture's quality map, rebuilt with the product's builders (pcc_b200.qmap) and checked
+    against the features the generator stored."""
+    kind = g["qkind"].tolist()
+    qg, qa = float(g["q"][0]), float(g["q"][1])
+    if not kind:
+        qc, qf = pcc.qmap.q_map(x, qg, qa)
+    elif kind[0] == 0.0:
+        qc, qf = pcc.qmap.view_q_map(x, qg, qa, int(kind[1]), kind[2], kind[3])
+    else:
+        qc, qf = pcc.qmap.roi_q_map(x, qg, qa, int(kind[1]), kind[2])
+    assert np.array_equal(qf.numpy().view(np.uint32), g["qf"].view(np.uint32))
+    return qc, qf
 
 
 @pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p) for p in GOLDEN])
@@ -33,7 +48,7 @@ def test_oracle_reproduces_reference_code_outputs(pcc, oracle, path):
     pcc.init_synthetic(model, int(g["seed"]))
     oc = oracle.OracleCodec(pcc.export_params(model), cfg)
     x = torch.from_numpy(g["x"])
-    qc, qf = pcc.synthetic.uniform_q_map(x, float(g["q"][0]), float(g["q"][1]))
+    qc, qf = _qmap(pcc, g, x)
     strings, shape, k, coords = oc.compress(g["x"], qc.numpy(), qf.numpy())
     assert strings[0][0] == g["y_string"].tobytes(), "y bitstream differs from the reference code's"
     assert strings[1][0] == g["z_string"].tobytes(), "z bitstream differs from the reference code's"
@@ -55,7 +70,7 @@ def test_product_reproduces_reference_code_outputs(pcc, path):
     model.eval().to(dev)
     model.update()
     x = torch.from_numpy(g["x"])
-    qc, qf = pcc.synthetic.uniform_q_map(x, float(g["q"][0]), float(g["q"][1]))
+    qc, qf = _qmap(pcc, g, x)
     strings, shape, k, coords = model.compress(x.to(dev), (qc.to(dev), qf.to(dev)))
     assert strings[0][0] == g["y_string"].tobytes(), "y bitstream differs from the reference code's"
     assert strings[1][0] == g["z_string"].tobytes(), "z bitstream differs from the reference code's"
