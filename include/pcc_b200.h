@@ -99,12 +99,23 @@ int pcc_coords_expand(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, 
  * sorted by (row / seg_rows, neighbour mask), so that rows with the same neighbour pattern share
  * a tile and the convolution skips the offsets a tile does not have (the reference's ME kernel
  * map keeps per-offset pair lists for the same purpose).  seg_rows: power of two >= PCC_TILE_M.
+ * n_groups (1 <= n_groups <= K; > 1 needs order): the K offsets are cut into n_groups consecutive
+ * ranges of ceil(K / n_groups) offsets and EACH range gets its own tile-row permutation, sorted by
+ * that range's bits of the neighbour mask — ragged maps (rows with unrelated neighbour patterns)
+ * then still form tiles whose rows agree on a 9-offset range.  order is [n_groups x n_out], tapmask
+ * [n_groups x ceil(n_out / PCC_TILE_M)] (group g's masks carry only its own offsets' bits), and
+ * nbr[k] is indexed by the tile rows of k's group.  pcc_conv_fwd then runs one pass per group,
+ * continuing every output element's FMA chain from the previous pass, so results do not change.
+ * n_groups == 0 chooses: the rows are sorted by the whole mask, the share of useful MACs of such
+ * tiles is measured on the device, and one group is kept when it is >= 0.85, else 3 groups are
+ * built; order / tapmask must be sized for 3 groups and the stream is synchronised to read the
+ * measurement.  *n_groups_used [host, may be NULL unless n_groups == 0] receives the group count.
  * ws: pcc_kernel_map_ws_bytes(n_out) bytes of scratch, needed only with order. */
 size_t pcc_kernel_map_ws_bytes(int64_t n_out);
 int pcc_kernel_map(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, const uint64_t* out_keys,
                    int64_t n_out, int kernel_size, int32_t step, int32_t in_align, int32_t* nbr,
-                   int64_t nbr_stride, uint32_t* tapmask, int32_t* order, int64_t seg_rows, void* ws,
-                   size_t ws_bytes, void* stream);
+                   int64_t nbr_stride, uint32_t* tapmask, int32_t* order, int64_t seg_rows,
+                   int32_t n_groups, int32_t* n_groups_used, void* ws, size_t ws_bytes, void* stream);
 
 /* ------------------------------------------------------------------ sparse convolution
  * Replaces ME convolution_kernel.cu / convolution_transpose_gpu.cu behind ME.MinkowskiConvolution
@@ -138,7 +149,7 @@ typedef struct pcc_conv_args {
   const float* bias;        /* [dev, cout] or NULL */
   const int32_t* nbr;       /* [dev, K x nbr_stride] */
   int64_t nbr_stride;
-  const uint32_t* tapmask;  /* [dev, ceil(n_out / PCC_TILE_M)] or NULL (= all taps) */
+  const uint32_t* tapmask;  /* [dev, n_groups x ceil(n_out / PCC_TILE_M)] or NULL (= all taps) */
   int32_t K;
   int32_t act;              /* PCC_ACT_* */
   float slope;              /* leaky slope */
@@ -153,7 +164,9 @@ typedef struct pcc_conv_args {
   int32_t mode;             /* PCC_MODE_* */
   int32_t flags;            /* PCC_CONV_* bit set */
   const float* weight_t;    /* [dev, K x cout x cin] (pcc_weight_transpose); required by PCC_MODE_TF32 */
-  const int32_t* order;     /* [dev, n_out] tile row -> output row (pcc_kernel_map), NULL = identity */
+  const int32_t* order;     /* [dev, n_groups x n_out] tile row -> output row (pcc_kernel_map), NULL = identity */
+  int32_t n_groups;         /* offset groups of the kernel map (0 or 1: one); > 1: PCC_MODE_EXACT only */
+  int32_t reserved;         /* 0 */
 } pcc_conv_args;
 
 int pcc_conv_fwd(const pcc_conv_args* args, void* stream);

@@ -19,7 +19,9 @@ extern "C" int pcc_conv_fwd(const pcc_conv_args* a, void* stream) {
   PCC_REQUIRE(a->act >= PCC_ACT_NONE && a->act <= PCC_ACT_LEAKY, "bad activation");
   cudaStream_t st = (cudaStream_t)stream;
   if (a->mode == PCC_MODE_EXACT) return pcc::conv_exact(a, st);
+  PCC_REQUIRE(a->n_groups <= 1 || (a->order && a->n_groups <= a->K), "n_groups > 1 needs order and n_groups <= K");
   if (a->mode == PCC_MODE_TF32) {
+    PCC_REQUIRE(a->n_groups <= 1, "PCC_MODE_TF32 takes kernel maps built with n_groups == 1");
     if (!pcc::conv_tf32_supported(a)) {
       pcc::set_error("pcc_conv_fwd: PCC_MODE_TF32 needs cin %% 32 == 0 and cout %% 32 == 0, 32 <= cout <= 256 (got %d -> %d)",
                      a->cin, a->cout);

@@ -47,6 +47,10 @@ struct ConvParams {
   int64_t nbr_stride, n_out, out_stride;
   int cin, cout, K, act, film_c, flags;
   float slope;
+  // offset group of this launch (kernel maps with n_groups > 1: one launch per group, chained through
+  // `out`, which holds the raw fp32 partial sums between the launches)
+  uint32_t kbits;   // offsets this launch may touch
+  int first, last;  // first: accumulators start at 0; last: epilogue applied
 };
 
 // bias -> activation -> FiLM -> residual -> (tf32 rounding) -> store, one output element
@@ -118,9 +122,9 @@ conv_exact_kernel(const ConvParams p) {
   const int64_t tile_base = (int64_t)blockIdx.x * CE_TM;
   const int co_base = blockIdx.y * TN;
   const int nchunks = (p.cin + CE_TK - 1) / CE_TK;
-  const uint32_t kfull = p.K >= 32 ? 0xffffffffu : ((1u << p.K) - 1u);
-  const uint32_t mask = p.tapmask ? (p.tapmask[blockIdx.x] & kfull) : kfull;
+  const uint32_t mask = p.tapmask ? (p.tapmask[blockIdx.x] & p.kbits) : p.kbits;
   const int nsteps = __popc(mask) * nchunks;
+  if (nsteps == 0 && !p.first && !p.last) return;  // nothing to add to the partial sums of this tile
 
   float acc[8][CN];
   unsigned long long acc2[8][CP];
@@ -130,6 +134,25 @@ conv_exact_kernel(const ConvParams p) {
     for (int c = 0; c < CN; ++c) acc[i][c] = 0.0f;
 #pragma unroll
     for (int c = 0; c < CP; ++c) acc2[i][c] = 0ull;
+  }
+  if (!p.first) {  // continue the FMA chains from the previous group's partial sums
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int64_t t = tile_base + rbase + 4 * i;
+      if (t >= p.n_out) continue;
+      const int64_t o = p.order ? (int64_t)__ldg(p.order + t) : t;
+#pragma unroll
+      for (int c = 0; c < CN; ++c) {
+        const int col = co_base + cbase + ((CN == 8) ? ((c >> 2) * 32 + (c & 3)) : c);
+        if (col < p.cout) acc[i][c] = p.out[o * p.out_stride + col];
+      }
+    }
+    if (PK) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int c = 0; c < CP; ++c) acc2[i][c] = pack2(acc[i][(2 * c) % CN], acc[i][(2 * c + 1) % CN]);
+    }
   }
 
   // producer cursor.  The kernel-map rows of the current offset (idx) and of the next active
@@ -301,7 +324,11 @@ conv_exact_kernel(const ConvParams p) {
 #pragma unroll
     for (int c = 0; c < CN; ++c) {
       const int col = co_base + cbase + ((CN == 8) ? ((c >> 2) * 32 + (c & 3)) : c);
-      if (col < p.cout) conv_epilogue(p, o, frow, rrow, col, acc[i][c]);
+      if (col >= p.cout) continue;
+      if (p.last)
+        conv_epilogue(p, o, frow, rrow, col, acc[i][c]);
+      else
+        p.out[o * p.out_stride + col] = acc[i][c];
     }
   }
 }
@@ -326,9 +353,9 @@ conv_head_kernel(const ConvParams p) {
   const int tid = threadIdx.x;
   const int64_t tile_base = (int64_t)blockIdx.x * CE_TM;
   const int nchunks = (p.cin + CE_TK - 1) / CE_TK;
-  const uint32_t kfull = p.K >= 32 ? 0xffffffffu : ((1u << p.K) - 1u);
-  const uint32_t mask = p.tapmask ? (p.tapmask[blockIdx.x] & kfull) : kfull;
+  const uint32_t mask = p.tapmask ? (p.tapmask[blockIdx.x] & p.kbits) : p.kbits;
   const int nsteps = __popc(mask) * nchunks;
+  if (nsteps == 0 && !p.first && !p.last) return;
 
   uint32_t pmask = mask;
   int pk = pmask ? (__ffs(pmask) - 1) : 0;
@@ -387,6 +414,13 @@ conv_head_kernel(const ConvParams p) {
   }
 
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  if (!p.first && tid < CE_TM && tile_base + tid < p.n_out) {
+    const int64_t t = tile_base + tid;
+    const int64_t o = p.order ? (int64_t)__ldg(p.order + t) : t;
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      if (c < p.cout) acc[c] = p.out[o * p.out_stride + c];
+  }
   for (int s = 0; s < nsteps; ++s) {
     cp_async_wait<CH_STAGES - 2>();
     __syncthreads();
@@ -418,8 +452,13 @@ conv_head_kernel(const ConvParams p) {
   if (p.film_c && p.film_rows) frow = __ldg(p.film_rows + o);
   if (p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
 #pragma unroll
-  for (int c = 0; c < 4; ++c)
-    if (c < p.cout) conv_epilogue(p, o, frow, rrow, c, acc[c]);
+  for (int c = 0; c < 4; ++c) {
+    if (c >= p.cout) continue;
+    if (p.last)
+      conv_epilogue(p, o, frow, rrow, c, acc[c]);
+    else
+      p.out[o * p.out_stride + c] = acc[c];
+  }
 }
 
 static int launch_head(const ConvParams& p, cudaStream_t st) {
@@ -463,12 +502,7 @@ static int launch_exact(const ConvParams& p, cudaStream_t st) {
   return vec ? launch_exact_v<TN, true, 0>(p, st) : launch_exact_v<TN, false, 0>(p, st);
 }
 
-int conv_exact(const pcc_conv_args* a, cudaStream_t st) {
-  ConvParams p;
-  p.in = a->in; p.weight = a->weight; p.bias = a->bias; p.nbr = a->nbr; p.tapmask = a->tapmask;
-  p.film = a->film; p.film_rows = a->film_rows; p.residual = a->residual; p.res_rows = a->res_rows;
-  p.order = a->order; p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
-  p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope; p.flags = a->flags;
+static int conv_exact_group(const pcc_conv_args* a, const ConvParams& p, cudaStream_t st) {
   if (a->cout <= 4 && a->cin % 4 == 0 && a->cin >= 16 && (reinterpret_cast<uintptr_t>(p.in) & 15) == 0)
     return launch_head(p, st);
   // a grid that cannot fill 2 CTAs on every SM is split further along the output channels
@@ -478,6 +512,33 @@ int conv_exact(const pcc_conv_args* a, cudaStream_t st) {
   if (a->cout > 32) return launch_exact<64>(p, st);
   if (a->cout > 16) return launch_exact<32>(p, st);
   return launch_exact<16>(p, st);
+}
+
+int conv_exact(const pcc_conv_args* a, cudaStream_t st) {
+  ConvParams p;
+  p.in = a->in; p.weight = a->weight; p.bias = a->bias; p.nbr = a->nbr; p.tapmask = a->tapmask;
+  p.film = a->film; p.film_rows = a->film_rows; p.residual = a->residual; p.res_rows = a->res_rows;
+  p.order = a->order; p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
+  p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope; p.flags = a->flags;
+  const uint32_t kfull = p.K >= 32 ? 0xffffffffu : ((1u << p.K) - 1u);
+  const int ng = a->n_groups > 1 ? a->n_groups : 1;
+  if (ng == 1) {
+    p.kbits = kfull; p.first = 1; p.last = 1;
+    return conv_exact_group(a, p, st);
+  }
+  // one launch per offset group: group g's tile rows follow order[g], its tap masks tapmask[g]
+  const int64_t tiles = ceil_div(p.n_out, CE_TM);
+  const int per = (p.K + ng - 1) / ng;
+  for (int g = 0; g < ng; ++g) {
+    const int k_lo = g * per, k_hi = (g + 1) * per < p.K ? (g + 1) * per : p.K;
+    p.kbits = (((k_hi >= 32) ? 0xffffffffu : ((1u << k_hi) - 1u)) & ~((1u << k_lo) - 1u)) & kfull;
+    p.first = g == 0; p.last = g == ng - 1;
+    p.order = a->order + (int64_t)g * p.n_out;
+    p.tapmask = a->tapmask ? a->tapmask + (int64_t)g * tiles : nullptr;
+    const int rc = conv_exact_group(a, p, st);
+    if (rc) return rc;
+  }
+  return PCC_OK;
 }
 
 }  // namespace pcc

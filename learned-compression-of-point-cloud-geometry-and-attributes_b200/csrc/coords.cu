@@ -216,13 +216,16 @@ __global__ void expand_emit_kernel(const uint64_t* __restrict__ keys, int64_t n,
 // (row / seg_rows, 27-bit neighbour mask), i.e. rows with the same neighbour pattern share tiles
 // while a tile's gathers stay inside one L2-sized segment of the map.  Pass 1 (MASK_ONLY) computes
 // the sort keys, a radix sort yields `order`, pass 2 writes nbr / tapmask in tile-row order.
+// MASK_ONLY: one thread per output row (natural order) -> its neighbour mask over all K offsets.
+// Otherwise: one thread per TILE ROW j of offset group [k_lo, k_hi): output row o = order[j], writes
+// nbr[k][j] for the group's offsets and the tile's tap mask (bits k_lo .. k_hi - 1 only).
 template <int KS, bool MASK_ONLY>
 __global__ void __launch_bounds__(PCC_TILE_M)
 kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict__ tvals,
                   uint64_t cap_mask, const uint64_t* __restrict__ out_keys, int64_t n_out, int step,
                   int in_align, const int32_t* __restrict__ order, int32_t* __restrict__ nbr,
-                  int64_t nbr_stride, uint32_t* __restrict__ tapmask, uint64_t* __restrict__ sort_keys,
-                  int seg_shift) {
+                  int64_t nbr_stride, uint32_t* __restrict__ tapmask, uint32_t* __restrict__ row_masks,
+                  int k_lo, int k_hi) {
   constexpr int K = KS * KS * KS;
   constexpr int LO = (KS == 3) ? -1 : 0;
   __shared__ uint32_t smask;
@@ -241,6 +244,7 @@ kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict_
   const int amask = in_align - 1;  // in_align is a power of two
 #pragma unroll 3
   for (int k = 0; k < K; ++k) {
+    if (!MASK_ONLY && (k < k_lo || k >= k_hi)) continue;
     const int dx = k % KS + LO, dy = (k / KS) % KS + LO, dz = k / (KS * KS) + LO;
     const int qx = x + dx * step, qy = y + dy * step, qz = z + dz * step;
     int r = -1;
@@ -251,7 +255,7 @@ kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict_
     if (r >= 0) mine |= 1u << k;
   }
   if (MASK_ONLY) {
-    if (live) sort_keys[j] = ((uint64_t)(j >> seg_shift) << 27) | mine;
+    if (live) row_masks[j] = mine;
     return;
   }
 #pragma unroll
@@ -259,6 +263,16 @@ kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict_
   if ((threadIdx.x & 31) == 0 && mine) atomicOr(&smask, mine);
   __syncthreads();
   if (threadIdx.x == 0 && tapmask) tapmask[blockIdx.x] = smask;
+}
+
+// sort key of row j for one offset group: (j / seg_rows, the group's bits of the row's neighbour mask)
+__global__ void group_key_kernel(const uint32_t* __restrict__ row_masks, int64_t n, int k_lo, int k_hi, int seg_shift,
+                                 uint64_t* __restrict__ keys, int32_t* __restrict__ iota) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const uint32_t sub = (row_masks[j] >> k_lo) & ((1u << (k_hi - k_lo)) - 1u);
+  keys[j] = ((uint64_t)(j >> seg_shift) << (k_hi - k_lo)) | sub;
+  iota[j] = (int32_t)j;
 }
 
 // ---------------------------------------------------------------- sort helpers
@@ -487,41 +501,111 @@ int pcc_coords_expand(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, 
 
 size_t pcc_kernel_map_ws_bytes(int64_t n_out) {
   if (n_out <= 0) return 256;
-  // sort keys in | sort keys out | iota | cub
-  return align_up((size_t)n_out * 8, 256) * 2 + align_up((size_t)n_out * 4, 256) +
-         align_up(cub_sort_pairs_bytes(n_out), 256);
+  // sort keys in | sort keys out | iota | row masks | cub | two counters
+  return align_up((size_t)n_out * 8, 256) * 2 + align_up((size_t)n_out * 4, 256) * 2 +
+         align_up(cub_sort_pairs_bytes(n_out), 256) + 256;
 }
 
 }  // extern "C"
 
+// useful[0] += pairs of the tile, useful[1] += 128 * offsets the tile would compute (tile rows = order)
+__global__ void __launch_bounds__(PCC_TILE_M)
+tile_efficiency_kernel(const uint32_t* __restrict__ row_masks, const int32_t* __restrict__ order, int64_t n,
+                       unsigned long long* __restrict__ sums) {
+  __shared__ uint32_t s_or;
+  __shared__ int s_pairs;
+  if (threadIdx.x == 0) {
+    s_or = 0;
+    s_pairs = 0;
+  }
+  __syncthreads();
+  const int64_t j = (int64_t)blockIdx.x * PCC_TILE_M + threadIdx.x;
+  uint32_t m = j < n ? row_masks[order[j]] : 0u;
+  int pc = __popc(m);
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) {
+    m |= __shfl_xor_sync(0xffffffffu, m, s);
+    pc += __shfl_xor_sync(0xffffffffu, pc, s);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicOr(&s_or, m);
+    atomicAdd(&s_pairs, pc);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    atomicAdd(sums, (unsigned long long)s_pairs);
+    atomicAdd(sums + 1, (unsigned long long)(PCC_TILE_M * __popc(s_or)));
+  }
+}
+
+// n_groups == 0 (automatic): single-group tiles are kept when at least this share of their MACs is useful
+constexpr double AUTO_GROUP_MIN_EFFICIENCY = 0.85;
+constexpr int AUTO_GROUPS = 3;
+
 template <int KS>
 static int kernel_map_launch(const uint64_t* tkeys, const int32_t* tvals, uint64_t cm, const uint64_t* out_keys,
                              int64_t n_out, int32_t step, int32_t in_align, int32_t* nbr, int64_t nbr_stride,
-                             uint32_t* tapmask, int32_t* order, int64_t seg_rows, void* ws, size_t ws_bytes,
-                             cudaStream_t st) {
+                             uint32_t* tapmask, int32_t* order, int64_t seg_rows, int32_t n_groups,
+                             int32_t* n_groups_used, void* ws, size_t ws_bytes, cudaStream_t st) {
+  constexpr int K = KS * KS * KS;
+  if (n_groups_used) *n_groups_used = n_groups > 0 ? n_groups : 1;
   const unsigned grid = (unsigned)ceil_div(n_out, PCC_TILE_M);
-  if (order) {
-    int seg_shift = 0;
-    while (((int64_t)1 << seg_shift) < seg_rows) ++seg_shift;
-    int seg_bits = 0;
-    while ((((n_out - 1) >> seg_shift) >> seg_bits) > 0) ++seg_bits;
-    char* w = reinterpret_cast<char*>(ws);
-    uint64_t* k_in = reinterpret_cast<uint64_t*>(w);
-    uint64_t* k_out = reinterpret_cast<uint64_t*>(w + align_up((size_t)n_out * 8, 256));
-    int32_t* iota = reinterpret_cast<int32_t*>(w + 2 * align_up((size_t)n_out * 8, 256));
-    void* cub_ws = w + 2 * align_up((size_t)n_out * 8, 256) + align_up((size_t)n_out * 4, 256);
-    size_t cub_bytes = align_up(cub_sort_pairs_bytes(n_out), 256);
-    kernel_map_kernel<KS, true><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align,
-                                                            nullptr, nullptr, 0, nullptr, k_in, seg_shift);
-    PCC_CHECK_LAUNCH("kernel_map_kernel<mask>");
-    iota_kernel<<<grid_for(n_out), THREADS, 0, st>>>(iota, n_out);
-    PCC_CHECK_LAUNCH("iota_kernel");
-    PCC_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(cub_ws, cub_bytes, k_in, k_out, iota, order, (int)n_out, 0,
-                                                   27 + seg_bits, st));
+  if (!order) {
+    kernel_map_kernel<KS, false><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align,
+                                                             nullptr, nbr, nbr_stride, tapmask, nullptr, 0, K);
+    PCC_CHECK_LAUNCH("kernel_map_kernel");
+    return PCC_OK;
   }
-  kernel_map_kernel<KS, false><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align,
-                                                           order, nbr, nbr_stride, tapmask, nullptr, 0);
-  PCC_CHECK_LAUNCH("kernel_map_kernel");
+  int seg_shift = 0;
+  while (((int64_t)1 << seg_shift) < seg_rows) ++seg_shift;
+  int seg_bits = 0;
+  while ((((n_out - 1) >> seg_shift) >> seg_bits) > 0) ++seg_bits;
+  char* w = reinterpret_cast<char*>(ws);
+  uint64_t* k_in = reinterpret_cast<uint64_t*>(w);
+  uint64_t* k_out = reinterpret_cast<uint64_t*>(w + align_up((size_t)n_out * 8, 256));
+  int32_t* iota = reinterpret_cast<int32_t*>(w + 2 * align_up((size_t)n_out * 8, 256));
+  uint32_t* row_masks = reinterpret_cast<uint32_t*>(w + 2 * align_up((size_t)n_out * 8, 256) + align_up((size_t)n_out * 4, 256));
+  void* cub_ws = w + 2 * align_up((size_t)n_out * 8, 256) + 2 * align_up((size_t)n_out * 4, 256);
+  size_t cub_bytes = align_up(cub_sort_pairs_bytes(n_out), 256);
+  kernel_map_kernel<KS, true><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align,
+                                                          nullptr, nullptr, 0, nullptr, row_masks, 0, K);
+  PCC_CHECK_LAUNCH("kernel_map_kernel<mask>");
+  bool have_order0 = false;
+  if (n_groups == 0) {
+    // sort by the whole mask, measure how well such tiles would be used, decide
+    unsigned long long* sums = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(cub_ws) + cub_bytes);
+    PCC_CHECK_CUDA(cudaMemsetAsync(sums, 0, 16, st));
+    group_key_kernel<<<grid_for(n_out), THREADS, 0, st>>>(row_masks, n_out, 0, K, seg_shift, k_in, iota);
+    PCC_CHECK_LAUNCH("group_key_kernel");
+    PCC_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(cub_ws, cub_bytes, k_in, k_out, iota, order, (int)n_out, 0,
+                                                   K + seg_bits, st));
+    tile_efficiency_kernel<<<grid, PCC_TILE_M, 0, st>>>(row_masks, order, n_out, sums);
+    PCC_CHECK_LAUNCH("tile_efficiency_kernel");
+    unsigned long long hbuf[2] = {0, 0};
+    unsigned long long* h = pinned_counts() ? reinterpret_cast<unsigned long long*>(pinned_counts()) : hbuf;
+    PCC_CHECK_CUDA(cudaMemcpyAsync(h, sums, 16, cudaMemcpyDeviceToHost, st));
+    PCC_CHECK_CUDA(cudaStreamSynchronize(st));
+    const bool single = K < AUTO_GROUPS || (double)h[0] >= AUTO_GROUP_MIN_EFFICIENCY * (double)h[1];
+    n_groups = single ? 1 : AUTO_GROUPS;
+    have_order0 = single;
+    if (n_groups_used) *n_groups_used = n_groups;
+  }
+  const int per = (K + n_groups - 1) / n_groups;
+  for (int g = 0; g < n_groups; ++g) {
+    const int k_lo = g * per, k_hi = (g + 1) * per < K ? (g + 1) * per : K;
+    int32_t* order_g = order + (int64_t)g * n_out;
+    if (!have_order0) {
+      group_key_kernel<<<grid_for(n_out), THREADS, 0, st>>>(row_masks, n_out, k_lo, k_hi, seg_shift, k_in, iota);
+      PCC_CHECK_LAUNCH("group_key_kernel");
+      PCC_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(cub_ws, cub_bytes, k_in, k_out, iota, order_g, (int)n_out, 0,
+                                                     (k_hi - k_lo) + seg_bits, st));
+    }
+    kernel_map_kernel<KS, false><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align,
+                                                             order_g, nbr, nbr_stride,
+                                                             tapmask ? tapmask + (int64_t)g * grid : nullptr, nullptr,
+                                                             k_lo, k_hi);
+    PCC_CHECK_LAUNCH("kernel_map_kernel");
+  }
   return PCC_OK;
 }
 
@@ -529,14 +613,18 @@ extern "C" {
 
 int pcc_kernel_map(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, const uint64_t* out_keys,
                    int64_t n_out, int kernel_size, int32_t step, int32_t in_align, int32_t* nbr,
-                   int64_t nbr_stride, uint32_t* tapmask, int32_t* order, int64_t seg_rows, void* ws,
-                   size_t ws_bytes, void* stream) {
+                   int64_t nbr_stride, uint32_t* tapmask, int32_t* order, int64_t seg_rows, int32_t n_groups,
+                   int32_t* n_groups_used, void* ws, size_t ws_bytes, void* stream) {
+  if (n_groups_used) *n_groups_used = n_groups > 0 ? n_groups : 1;
   if (n_out == 0) return PCC_OK;
   PCC_REQUIRE(tkeys && tvals && out_keys && nbr, "null pointer");
   PCC_REQUIRE(n_out < (1ll << 31), "n_out out of range");
   PCC_REQUIRE(nbr_stride >= n_out, "nbr_stride < n_out");
   PCC_REQUIRE(in_align > 0 && (in_align & (in_align - 1)) == 0, "in_align must be a power of two");
   PCC_REQUIRE((cap & (cap - 1)) == 0, "capacity must be a power of two");
+  PCC_REQUIRE(n_groups >= 0 && n_groups <= kernel_size * kernel_size * kernel_size, "n_groups out of range");
+  PCC_REQUIRE(n_groups == 1 || order, "n_groups != 1 needs an order array");
+  PCC_REQUIRE(n_groups != 0 || n_groups_used, "automatic n_groups needs n_groups_used");
   if (order) {
     PCC_REQUIRE(seg_rows >= PCC_TILE_M && (seg_rows & (seg_rows - 1)) == 0, "seg_rows must be a power of two >= 128");
     PCC_REQUIRE(ws && ws_bytes >= pcc_kernel_map_ws_bytes(n_out), "workspace too small");
@@ -545,11 +633,11 @@ int pcc_kernel_map(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, con
   const uint64_t cm = (uint64_t)cap - 1;
   switch (kernel_size) {
     case 1:
-      return kernel_map_launch<1>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask, order, seg_rows, ws, ws_bytes, st);
+      return kernel_map_launch<1>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask, order, seg_rows, n_groups, n_groups_used, ws, ws_bytes, st);
     case 2:
-      return kernel_map_launch<2>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask, order, seg_rows, ws, ws_bytes, st);
+      return kernel_map_launch<2>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask, order, seg_rows, n_groups, n_groups_used, ws, ws_bytes, st);
     case 3:
-      return kernel_map_launch<3>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask, order, seg_rows, ws, ws_bytes, st);
+      return kernel_map_launch<3>(tkeys, tvals, cm, out_keys, n_out, step, in_align, nbr, nbr_stride, tapmask, order, seg_rows, n_groups, n_groups_used, ws, ws_bytes, st);
     default:
       PCC_REQUIRE(false, "kernel_size must be 1, 2 or 3");
   }

@@ -4,6 +4,7 @@ torch is plumbing here (device memory, streams); every computation is a ``pcc_*`
 libpcc_b200.so.  There is no CPU fallback: tensors must live on a CUDA device.
 """
 import ctypes
+import os
 import weakref
 
 import torch
@@ -87,13 +88,20 @@ def sort_keys(keys, want_perm=True):
 
 
 class KernelMap:
-    """nbr [K, stride] int32 (offset-major, indexed by TILE ROW), tapmask [ceil(n_out/128)] uint32
-    (as int32), order [n_out] int32: tile row -> output row (None = identity)."""
-    __slots__ = ("nbr", "tapmask", "K", "n_out", "stride", "order", "_pairs_cache")
+    """nbr [K, stride] int32 (offset-major, indexed by TILE ROW of the offset's group), tapmask
+    [n_groups * ceil(n_out/128)] uint32 (as int32), order [n_groups, n_out] int32: tile row -> output
+    row (None = identity).  n_groups > 1: the K offsets are cut into consecutive ranges, each with its
+    own tile-row permutation (include/pcc_b200.h, pcc_kernel_map)."""
+    __slots__ = ("nbr", "tapmask", "K", "n_out", "stride", "order", "n_groups", "_pairs_cache")
 
-    def __init__(self, nbr, tapmask, K, n_out, stride, order=None):
+    def __init__(self, nbr, tapmask, K, n_out, stride, order=None, n_groups=1):
         self.nbr, self.tapmask, self.K, self.n_out, self.stride = nbr, tapmask, K, n_out, stride
-        self.order = order
+        self.order, self.n_groups = order, n_groups
+
+    def group_ranges(self):
+        """[(k_lo, k_hi)] of the offset groups."""
+        per = (self.K + self.n_groups - 1) // self.n_groups
+        return [(g * per, min((g + 1) * per, self.K)) for g in range(self.n_groups)]
 
     def natural_nbr(self):
         """nbr re-indexed by output row ([K, n_out]); what the oracle's kernel map holds."""
@@ -101,7 +109,8 @@ class KernelMap:
         if self.order is None:
             return nbr
         out = torch.empty_like(nbr)
-        out[:, self.order.long()] = nbr
+        for g, (lo, hi) in enumerate(self.group_ranges()):
+            out[lo:hi, self.order.view(self.n_groups, -1)[g].long()] = nbr[lo:hi]
         return out
 
 
@@ -191,34 +200,48 @@ class CoordMap:
             self._derived[key] = CoordMap(out[:n_out.value].clone(), self.ts // 2, True)
         return self._derived[key]
 
-    def kernel_map(self, out_map, kernel_size, transpose=False):
+    def kernel_map(self, out_map, kernel_size, transpose=False, groups=None):
         """Kernel map from this (input) map to out_map.  conv: targets c_o + d*ts_in;
-        transpose: targets q - d*ts_out, probed only when aligned to ts_in."""
-        key = (id(out_map), kernel_size, transpose)
+        transpose: targets q - d*ts_out, probed only when aligned to ts_in.  groups: number of
+        offset groups (None = tap_groups(): by mode and size)."""
+        K = kernel_size ** 3
+        n_out = out_map.n
+        seg = tile_segment_rows()
+        ng = tap_groups(K, n_out) if groups is None else max(0, min(int(groups), K))  # 0 = measured choice
+        key = (id(out_map), kernel_size, transpose, ng, seg)
         km = self._kmaps.get(key)
         if km is not None and km[0]() is out_map:
             return km[1]
-        K = kernel_size ** 3
-        n_out = out_map.n
         stride = max(n_out, 1)
         nbr = torch.empty((K, stride), dtype=torch.int32, device=self.device)
-        tapmask = torch.empty(max((n_out + TILE_M - 1) // TILE_M, 1), dtype=torch.int32, device=self.device)
+        cap_g = ng if ng else AUTO_GROUPS
+        tiles = max((n_out + TILE_M - 1) // TILE_M, 1)
+        tapmask = torch.empty(cap_g * tiles, dtype=torch.int32, device=self.device)
         order = None
         if n_out:
             tk, tv, cap = self.hash()
             step = -out_map.ts if transpose else self.ts
             align = self.ts if transpose else 1
             ws, wsb = None, 0
-            seg = tile_segment_rows()
-            if K > 1 and n_out > TILE_M and seg:
-                order = torch.empty(n_out, dtype=torch.int32, device=self.device)
+            if not (K > 1 and n_out > TILE_M and seg):
+                ng = 1
+            else:
+                order = torch.empty(cap_g * n_out, dtype=torch.int32, device=self.device)
                 wsb = _L().pcc_kernel_map_ws_bytes(n_out)
                 ws = _ws(wsb, self.device)
+            used = ctypes.c_int32(1)
             check(_L().pcc_kernel_map(_ptr(tk), _ptr(tv), cap, _ptr(out_map.keys), n_out, kernel_size, step,
-                                      align, _ptr(nbr), stride, _ptr(tapmask), _ptr(order), seg,
-                                      _ptr(ws), wsb, _stream()), "pcc_kernel_map")
-            _count(1 if order is None else 7)
-        kmap = KernelMap(nbr, tapmask, K, n_out, stride, order)
+                                      align, _ptr(nbr), stride, _ptr(tapmask), _ptr(order), seg, ng,
+                                      ctypes.byref(used), _ptr(ws), wsb, _stream()), "pcc_kernel_map")
+            if ng == 0:
+                _count(6)
+            ng = used.value
+            if order is not None:
+                order, tapmask = order[:ng * n_out], tapmask[:ng * tiles]
+            _count(1 if order is None else 1 + 6 * ng)
+        else:
+            ng = 1
+        kmap = KernelMap(nbr, tapmask, K, n_out, stride, order, ng)
         # weak reference: out_map is often this map itself (stride-1 layers) or a map that caches the
         # transposed direction back to this one; a strong reference would make the pair collectable
         # only by the cycle collector and keep its kernel maps (K x n_out x 4 bytes) alive until then
@@ -244,6 +267,30 @@ def tile_segment_rows():
     if _tile_seg_rows is not None:
         return _tile_seg_rows
     return (1 << 30) if _default_mode == MODE_EXACT else (1 << 17)
+
+
+# Offset groups of the kernel maps (pcc_kernel_map n_groups).  None = by mode: the exact path lets the
+# library measure each 27-offset map (n_groups = 0): maps whose mask-sorted tiles use >= 85 % of
+# their MACs keep one group, ragged ones (e.g. the decoder's pruned sets under random-init weights,
+# 40-60 %) are cut into 3 groups of 9 offsets, each with its own mask-sorted tile rows (80-98 %), for
+# two extra launches per convolution.  The tensor-core kernel takes single-group maps only.
+_tap_groups = int(os.environ["PCC_TAP_GROUPS"]) if "PCC_TAP_GROUPS" in os.environ else None
+AUTO_GROUPS = 3
+
+
+def set_tap_groups(n):
+    """Force the number of offset groups of 27-offset kernel maps built afterwards (None = automatic).
+    Results are independent of it."""
+    global _tap_groups
+    _tap_groups = None if n is None else int(n)
+
+
+def tap_groups(K, n_out):
+    if K != 27:
+        return 1
+    if _tap_groups is not None:
+        return max(0, min(_tap_groups, K))
+    return 0 if (_default_mode == MODE_EXACT and n_out > TILE_M) else 1
 
 
 def make_map(coords_or_keys, ts=1, assume_sorted=False):
@@ -403,6 +450,10 @@ def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None
     a.mode = mode
     a.flags = CONV_ROUND_OUT_TF32 if round_out else 0
     a.order = None if kmap.order is None else kmap.order.data_ptr()
+    a.n_groups = kmap.n_groups
+    if mode == MODE_TF32 and kmap.n_groups > 1:
+        raise _lib.PccError("the tensor-core mode takes single-group kernel maps: build the map in tf32 mode "
+                            "or with set_tap_groups(1)")
     if _profile is not None and n_out:
         rec = {"cin": cin, "cout": cout, "K": K, "n_in": int(feats.shape[0]), "n_out": int(n_out),
                "pairs": _pairs(kmap), "mode": int(mode), "ev0": torch.cuda.Event(enable_timing=True),
@@ -411,11 +462,11 @@ def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None
         check(_L().pcc_conv_fwd(ctypes.byref(a), _stream()), "pcc_conv_fwd")
         rec["ev1"].record()
         _profile.append(rec)
-        _count()
+        _count(kmap.n_groups)
         return out
     check(_L().pcc_conv_fwd(ctypes.byref(a), _stream()), "pcc_conv_fwd")
     if n_out:
-        _count()
+        _count(kmap.n_groups)
     return out
 
 

@@ -260,10 +260,10 @@ class SlabMap:
     def lookup(self, q_keys):
         return self.full.lookup(q_keys)
 
-    def kernel_map(self, out_map, kernel_size, transpose=False):
+    def kernel_map(self, out_map, kernel_size, transpose=False, groups=None):
         """Inputs: every local row (owned + halo); outputs: out_map's owned rows."""
         out = out_map.own if isinstance(out_map, SlabMap) else out_map
-        return self.full.kernel_map(out, kernel_size, transpose=transpose)
+        return self.full.kernel_map(out, kernel_size, transpose=transpose, groups=groups)
 
     def stride2(self):
         if "s2" not in self._derived:

@@ -201,10 +201,12 @@ def test_color_finalize(pcc, oracle):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("seg", [0, 128, 1024, 1 << 17])
-def test_conv_independent_of_tile_order(pcc, oracle, seg):
-    """The tile-row permutation of the kernel map (rows grouped by neighbour mask) must not change
-    a single bit of the result, in either mode, with FiLM / residual row lookups in the epilogue."""
+@pytest.mark.parametrize("seg,groups", [(0, 1), (128, 1), (1024, 1), (1 << 17, 1), (128, 3), (1 << 17, 3), (1 << 30, 9),
+                                        (1 << 30, 27)])
+def test_conv_independent_of_tile_order(pcc, oracle, seg, groups):
+    """The tile-row permutation(s) of the kernel map (rows grouped by neighbour mask, per offset
+    group) must not change a single bit of the result, in either mode, with FiLM / residual row
+    lookups in the epilogue; grouped maps run one chained pass per group (exact mode only)."""
     ops = pcc.ops
     rng = np.random.default_rng(5)
     old = ops._tile_seg_rows
@@ -222,14 +224,23 @@ def test_conv_independent_of_tile_order(pcc, oracle, seg):
         ref = oracle.prims.relu(oracle.prims.conv_apply(x, nbr, W, b))
         g = np.where(frows[:, None] >= 0, film[np.maximum(frows, 0)], np.float32(0))
         ref = ((ref * g[:, :cout] + g[:, cout:]).astype(np.float32) + res).astype(np.float32)
-        km = m.kernel_map(m, 3)
-        assert (km.order is None) == (seg == 0)
+        km = m.kernel_map(m, 3, groups=groups)
+        assert (km.order is None) == (seg == 0) and km.n_groups == groups
         t = lambda a: torch.from_numpy(a).to(DEV)
         got = ops.conv(t(x), km, t(W), t(b), act=1, film=t(film), film_rows=t(frows), residual=t(res),
                        mode=ops.MODE_EXACT)
         assert np.array_equal(got.cpu().numpy().view(np.uint32), ref.view(np.uint32))
-        g32 = ops.conv(t(x), km, t(W), t(b), act=1, film=t(film), film_rows=t(frows), residual=t(res),
-                       mode=ops.MODE_TF32, round_out=False)
-        assert (g32 - got).abs().max().item() <= 2e-2
+        # narrow-output kernel over the same (grouped) map
+        W4 = np.ascontiguousarray(W[:, :, :3])
+        ref4 = oracle.prims.conv_apply(x, nbr, W4, np.ascontiguousarray(b[:, :3]))
+        got4 = ops.conv(t(x), km, t(W4), t(np.ascontiguousarray(b[:, :3])), mode=ops.MODE_EXACT)
+        assert np.array_equal(got4.cpu().numpy().view(np.uint32), ref4.astype(np.float32).view(np.uint32))
+        if groups == 1:
+            g32 = ops.conv(t(x), km, t(W), t(b), act=1, film=t(film), film_rows=t(frows), residual=t(res),
+                           mode=ops.MODE_TF32, round_out=False)
+            assert (g32 - got).abs().max().item() <= 2e-2
+        else:
+            with pytest.raises(pcc.PccError):
+                ops.conv(t(x), km, t(W), t(b), mode=ops.MODE_TF32)
     finally:
         ops.set_tile_segment_rows(old)

@@ -71,13 +71,15 @@ def test_kernel_map_properties_full_size(pcc, level0):
         assert torch.equal(back, rows[has])
         assert int(has.sum()) == int((nbr[26 - k] >= 0).sum())
     # the tile-row permutation is a permutation and the tap mask covers every pair of its tile
-    if km.order is not None:
-        assert torch.equal(torch.sort(km.order.long()).values, torch.arange(n, device=DEV))
     tiles = (n + 127) // 128
     pad = torch.full((27, tiles * 128 - n), -1, dtype=torch.int32, device=DEV)
     active = (torch.cat([km.nbr[:, :n], pad], 1).view(27, tiles, 128) >= 0).any(dim=2)
-    bits = ((km.tapmask.long().unsqueeze(0) >> torch.arange(27, device=DEV).unsqueeze(1)) & 1).bool()
-    assert torch.equal(bits, active)
+    assert km.n_groups == 1                                             # a surface: mask-sorted tiles are >= 85 % useful
+    for g, (lo, hi) in enumerate(km.group_ranges()):
+        assert torch.equal(torch.sort(km.order.view(km.n_groups, -1)[g].long()).values, torch.arange(n, device=DEV))
+        tm = km.tapmask.view(km.n_groups, -1)[g].long()
+        bits = ((tm.unsqueeze(0) >> torch.arange(27, device=DEV).unsqueeze(1)) & 1).bool()
+        assert torch.equal(bits[lo:hi], active[lo:hi]) and not bool(bits[:lo].any()) and not bool(bits[hi:].any())
 
 
 @pytest.mark.parametrize("cin,cout,mode", [(64, 64, 0), (128, 128, 0), (64, 4, 0), (128, 128, 1)])
@@ -89,7 +91,7 @@ def test_conv_scaling_property_full_size(pcc, level0, cin, cout, mode):
     if mode == 1:  # tf32 operands: keep them representable so scaling by 2 stays exact
         x = (x.view(torch.int32) & ~0x1FFF).view(torch.float32)
         W = (W.view(torch.int32) & ~0x1FFF).view(torch.float32)
-    km = m.kernel_map(m, 3)
+    km = m.kernel_map(m, 3, groups=1 if mode == 1 else None)
     a = pcc.ops.conv(x, km, W, None, mode=mode)
     b = pcc.ops.conv(2.0 * x, km, W, None, mode=mode)
     assert torch.isfinite(a).all()

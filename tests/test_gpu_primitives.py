@@ -89,9 +89,9 @@ def _oracle_sorted(oracle, c, ts):
     return keys, oracle.prims.unpack_keys(keys)
 
 
-@pytest.mark.parametrize("ks", [1, 2, 3])
+@pytest.mark.parametrize("ks,groups", [(1, None), (2, None), (3, 1), (3, 3), (3, 5)])
 @pytest.mark.parametrize("n,extent,ts", [(60, 6, 1), (7000, 35, 2), (150000, 150, 1)])
-def test_kernel_map_conv(pcc, oracle, ks, n, extent, ts):
+def test_kernel_map_conv(pcc, oracle, ks, groups, n, extent, ts):
     pcc.ops.set_tile_segment_rows(1 << 16 if n > 100000 else None)  # multi-segment case
     c = random_cloud(n, extent, 6, 1, -3)
     c[:, 1:] *= ts
@@ -99,28 +99,32 @@ def test_kernel_map_conv(pcc, oracle, ks, n, extent, ts):
     keys, cs = _oracle_sorted(oracle, c, ts)
     offs = oracle.prims.kernel_offsets(ks) * ts
     # stride 1
-    km = m.kernel_map(m, ks)
+    km = m.kernel_map(m, ks, groups=groups)
     ref = oracle.prims.kernel_map(keys, cs, offs)
     assert np.array_equal(km.natural_nbr().cpu().numpy(), ref)
-    # tile rows: `order` is a permutation (sorted by neighbour mask inside lexicographic segments)
-    # and the tap mask is the OR over the rows of each 128-row tile in that order
-    order = np.arange(ref.shape[1]) if km.order is None else km.order.cpu().numpy()
-    assert np.array_equal(np.sort(order), np.arange(ref.shape[1]))
-    tiled = ref[:, order]
-    assert np.array_equal(km.nbr[:, :km.n_out].cpu().numpy(), tiled)
-    if km.order is not None:
-        seg = pcc.ops.tile_segment_rows()
-        rowmask = ((ref >= 0).astype(np.int64) << np.arange(ref.shape[0])[:, None]).sum(0)
-        sortkey = ((np.arange(ref.shape[1]) // seg) << 27) | rowmask
-        assert np.array_equal(order, np.argsort(sortkey, kind="stable"))
-    tiles = (ref.shape[1] + 127) // 128
+    # tile rows: per offset group, `order` is a permutation (sorted by the group's bits of the neighbour
+    # mask inside lexicographic segments) and the tap mask is the OR over the rows of each 128-row tile
+    n_out = ref.shape[1]
+    tiles = (n_out + 127) // 128
     tm = km.tapmask.cpu().numpy().view(np.uint32)
-    for t in range(tiles):
-        want = 0
-        for k in range(ref.shape[0]):
-            if (tiled[k, t * 128:(t + 1) * 128] >= 0).any():
-                want |= 1 << k
-        assert tm[t] == want
+    nbr_t = km.nbr[:, :km.n_out].cpu().numpy()
+    assert km.n_groups == (1 if (groups is None or km.order is None) else groups)
+    for g, (lo, hi) in enumerate(km.group_ranges()):
+        order = np.arange(n_out) if km.order is None else km.order.view(km.n_groups, -1)[g].cpu().numpy()
+        assert np.array_equal(np.sort(order), np.arange(n_out))
+        tiled = ref[lo:hi][:, order]
+        assert np.array_equal(nbr_t[lo:hi], tiled)
+        if km.order is not None:
+            seg = pcc.ops.tile_segment_rows()
+            rowmask = ((ref[lo:hi] >= 0).astype(np.int64) << np.arange(hi - lo)[:, None]).sum(0)
+            sortkey = ((np.arange(n_out) // seg) << (hi - lo)) | rowmask
+            assert np.array_equal(order, np.argsort(sortkey, kind="stable"))
+        for t in range(tiles):
+            want = 0
+            for k in range(lo, hi):
+                if (tiled[k - lo, t * 128:(t + 1) * 128] >= 0).any():
+                    want |= 1 << k
+            assert tm[g * tiles + t] == want
     # stride 2
     s = m.stride2()
     km2 = m.kernel_map(s, ks)

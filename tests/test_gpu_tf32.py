@@ -27,7 +27,7 @@ def test_conv_tf32_close_to_exact(pcc, cin, cout, n):
     b = torch.from_numpy(rng.standard_normal((1, cout)).astype(np.float32)).to(DEV)
     film = torch.from_numpy(rng.standard_normal((m.n, 2 * cout)).astype(np.float32)).to(DEV)
     res = torch.from_numpy(rng.standard_normal((m.n, cout)).astype(np.float32)).to(DEV)
-    km = m.kernel_map(m, 3)
+    km = m.kernel_map(m, 3, groups=1)
     for kw in ({}, {"act": ops.ACT_RELU, "film": film, "residual": res}, {"act": ops.ACT_LEAKY}):
         ref = ops.conv(x, km, W, b, mode=ops.MODE_EXACT, **kw)
         got = ops.conv(x, km, W, b, mode=ops.MODE_TF32, **kw)
@@ -47,7 +47,7 @@ def test_conv_tf32_strided_and_transposed(pcc, ks, transpose):
     c[:, 1:] *= 4
     m, _ = ops.canonical_map(torch.from_numpy(c).to(DEV), 4)
     out_map = m.expand(ks) if transpose else m.stride2()
-    km = m.kernel_map(out_map, ks, transpose=transpose)
+    km = m.kernel_map(out_map, ks, transpose=transpose, groups=1)
     xi = torch.randint(-4, 5, (m.n, 64), device=DEV).float()
     Wi = torch.randint(-2, 3, (ks ** 3, 64, 128), device=DEV).float()
     assert torch.equal(ops.conv(xi, km, Wi, None, mode=ops.MODE_TF32), ops.conv(xi, km, Wi, None, mode=ops.MODE_EXACT))
@@ -61,7 +61,7 @@ def test_tf32_small_channels_take_exact_path(pcc):
     m, _ = ops.canonical_map(torch.from_numpy(c).to(DEV))
     x = torch.randn((m.n, 4), device=DEV)
     W = torch.randn((27, 4, 64), device=DEV)
-    km = m.kernel_map(m, 3)
+    km = m.kernel_map(m, 3, groups=1)
     ref = ops.conv(x, km, W, None, mode=ops.MODE_EXACT)
     assert torch.equal(ops.conv(x, km, W, None, mode=ops.MODE_TF32, round_out=False), ref)
     # by default tf32 mode stores activations rounded to tf32 (round-to-nearest, unbiased), so that
