@@ -107,15 +107,19 @@ int pcc_coords_expand(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, 
  * nbr[k] is indexed by the tile rows of k's group.  pcc_conv_fwd then runs one pass per group,
  * continuing every output element's FMA chain from the previous pass, so results do not change.
  * n_groups == 0 chooses: the rows are sorted by the whole mask, the share of useful MACs of such
- * tiles is measured on the device, and one group is kept when it is >= 0.85, else 3 groups are
+ * tiles is measured on the device, and one group is kept when it is >= 0.72, else 3 groups are
  * built; order / tapmask must be sized for 3 groups and the stream is synchronised to read the
  * measurement.  *n_groups_used [host, may be NULL unless n_groups == 0] receives the group count.
+ * tile_order [dev, n_groups x ceil(n_out / PCC_TILE_M), may be NULL; needs tapmask] RECEIVES, per
+ * group, the tiles sorted by descending number of active offsets: the convolution's CTA b works on
+ * tile tile_order[b], so the long tiles start first and the short ones fill the tail of the launch.
  * ws: pcc_kernel_map_ws_bytes(n_out) bytes of scratch, needed only with order. */
 size_t pcc_kernel_map_ws_bytes(int64_t n_out);
 int pcc_kernel_map(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, const uint64_t* out_keys,
                    int64_t n_out, int kernel_size, int32_t step, int32_t in_align, int32_t* nbr,
-                   int64_t nbr_stride, uint32_t* tapmask, int32_t* order, int64_t seg_rows,
-                   int32_t n_groups, int32_t* n_groups_used, void* ws, size_t ws_bytes, void* stream);
+                   int64_t nbr_stride, uint32_t* tapmask, int32_t* order, int32_t* tile_order,
+                   int64_t seg_rows, int32_t n_groups, int32_t* n_groups_used, void* ws, size_t ws_bytes,
+                   void* stream);
 
 /* ------------------------------------------------------------------ sparse convolution
  * Replaces ME convolution_kernel.cu / convolution_transpose_gpu.cu behind ME.MinkowskiConvolution
@@ -167,6 +171,7 @@ typedef struct pcc_conv_args {
   const int32_t* order;     /* [dev, n_groups x n_out] tile row -> output row (pcc_kernel_map), NULL = identity */
   int32_t n_groups;         /* offset groups of the kernel map (0 or 1: one); > 1: PCC_MODE_EXACT only */
   int32_t reserved;         /* 0 */
+  const int32_t* tile_order; /* [dev, n_groups x tiles] launch order of the tiles (pcc_kernel_map), NULL = identity */
 } pcc_conv_args;
 
 int pcc_conv_fwd(const pcc_conv_args* args, void* stream);

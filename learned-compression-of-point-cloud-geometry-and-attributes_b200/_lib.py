@@ -28,7 +28,7 @@ class ConvArgs(ctypes.Structure):
         ("K", I32), ("act", I32), ("slope", F32), ("film_c", I32),
         ("film", P), ("film_rows", P), ("residual", P), ("res_rows", P),
         ("out", P), ("n_out", I64), ("out_stride", I64), ("mode", I32), ("flags", I32),
-        ("weight_t", P), ("order", P), ("n_groups", I32), ("reserved", I32),
+        ("weight_t", P), ("order", P), ("n_groups", I32), ("reserved", I32), ("tile_order", P),
     ]
 
 
@@ -49,7 +49,7 @@ SIGNATURES = {
     "pcc_expand_ws_bytes": (SZ, [I64, I32]),
     "pcc_coords_expand": (I32, [P, P, I64, P, I64, I32, I32, P, P, P, SZ, P]),
     "pcc_kernel_map_ws_bytes": (SZ, [I64]),
-    "pcc_kernel_map": (I32, [P, P, I64, P, I64, I32, I32, I32, P, I64, P, P, I64, I32, P, P, SZ, P]),
+    "pcc_kernel_map": (I32, [P, P, I64, P, I64, I32, I32, I32, P, I64, P, P, P, I64, I32, P, P, SZ, P]),
     "pcc_conv_fwd": (I32, [P, P]),
     "pcc_weight_transpose": (I32, [P, I32, I32, I32, P, P]),
     "pcc_gather_rows": (I32, [P, I32, P, I64, P, P, P]),

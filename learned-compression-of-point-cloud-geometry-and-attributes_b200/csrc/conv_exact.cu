@@ -51,6 +51,7 @@ struct ConvParams {
   // `out`, which holds the raw fp32 partial sums between the launches)
   uint32_t kbits;   // offsets this launch may touch
   int first, last;  // first: accumulators start at 0; last: epilogue applied
+  const int32_t* tile_order;  // CTA b works on tile tile_order[b] (longest tiles first), NULL = identity
 };
 
 // bias -> activation -> FiLM -> residual -> (tf32 rounding) -> store, one output element
@@ -119,10 +120,11 @@ conv_exact_kernel(const ConvParams p) {
   const int tx = lane & 7, ty = lane >> 3;
   const int rbase = (wid >> 1) * 32 + ty;
   const int cbase = (wid & 1) * (TN / 2) + tx * (CN == 8 ? 4 : CN);
-  const int64_t tile_base = (int64_t)blockIdx.x * CE_TM;
+  const unsigned tile = p.tile_order ? (unsigned)__ldg(p.tile_order + blockIdx.x) : blockIdx.x;
+  const int64_t tile_base = (int64_t)tile * CE_TM;
   const int co_base = blockIdx.y * TN;
   const int nchunks = (p.cin + CE_TK - 1) / CE_TK;
-  const uint32_t mask = p.tapmask ? (p.tapmask[blockIdx.x] & p.kbits) : p.kbits;
+  const uint32_t mask = p.tapmask ? (p.tapmask[tile] & p.kbits) : p.kbits;
   const int nsteps = __popc(mask) * nchunks;
   if (nsteps == 0 && !p.first && !p.last) return;  // nothing to add to the partial sums of this tile
 
@@ -351,9 +353,10 @@ conv_head_kernel(const ConvParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   HeadSmem& sm = *reinterpret_cast<HeadSmem*>(smem_raw);
   const int tid = threadIdx.x;
-  const int64_t tile_base = (int64_t)blockIdx.x * CE_TM;
+  const unsigned tile = p.tile_order ? (unsigned)__ldg(p.tile_order + blockIdx.x) : blockIdx.x;
+  const int64_t tile_base = (int64_t)tile * CE_TM;
   const int nchunks = (p.cin + CE_TK - 1) / CE_TK;
-  const uint32_t mask = p.tapmask ? (p.tapmask[blockIdx.x] & p.kbits) : p.kbits;
+  const uint32_t mask = p.tapmask ? (p.tapmask[tile] & p.kbits) : p.kbits;
   const int nsteps = __popc(mask) * nchunks;
   if (nsteps == 0 && !p.first && !p.last) return;
 
@@ -521,6 +524,7 @@ int conv_exact(const pcc_conv_args* a, cudaStream_t st) {
   p.order = a->order; p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
   p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope; p.flags = a->flags;
   const uint32_t kfull = p.K >= 32 ? 0xffffffffu : ((1u << p.K) - 1u);
+  p.tile_order = a->tile_order;
   const int ng = a->n_groups > 1 ? a->n_groups : 1;
   if (ng == 1) {
     p.kbits = kfull; p.first = 1; p.last = 1;
@@ -535,6 +539,7 @@ int conv_exact(const pcc_conv_args* a, cudaStream_t st) {
     p.first = g == 0; p.last = g == ng - 1;
     p.order = a->order + (int64_t)g * p.n_out;
     p.tapmask = a->tapmask ? a->tapmask + (int64_t)g * tiles : nullptr;
+    p.tile_order = a->tile_order ? a->tile_order + (int64_t)g * tiles : nullptr;
     const int rc = conv_exact_group(a, p, st);
     if (rc) return rc;
   }

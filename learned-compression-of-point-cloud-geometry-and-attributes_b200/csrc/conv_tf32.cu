@@ -47,6 +47,7 @@ struct TcParams {
   const float* residual;
   const int32_t* res_rows;
   const int32_t* order;
+  const int32_t* tile_order;  // CTA b works on tile tile_order[b] (longest tiles first), NULL = identity
   float* out;
   int64_t nbr_stride, n_out, out_stride;
   int cin, cout, K, act, film_c, flags;
@@ -188,11 +189,12 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
-  const int64_t tile_base = (int64_t)blockIdx.x * TC_TM;
+  const unsigned tile = p.tile_order ? (unsigned)__ldg(p.tile_order + blockIdx.x) : blockIdx.x;
+  const int64_t tile_base = (int64_t)tile * TC_TM;
   const int co_base = blockIdx.y * BN;
   const int nchunks = p.cin / TC_TK;
   const uint32_t kfull = p.K >= 32 ? 0xffffffffu : ((1u << p.K) - 1u);
-  const uint32_t mask = p.tapmask ? (p.tapmask[blockIdx.x] & kfull) : kfull;
+  const uint32_t mask = p.tapmask ? (p.tapmask[tile] & kfull) : kfull;
   const int nsteps = __popc(mask) * nchunks;
   constexpr uint32_t TMEM_COLS = BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256));
 
@@ -466,11 +468,12 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
-  const int64_t tile_base = (int64_t)blockIdx.x * TC_TM;
+  const unsigned tile = p.tile_order ? (unsigned)__ldg(p.tile_order + blockIdx.x) : blockIdx.x;
+  const int64_t tile_base = (int64_t)tile * TC_TM;
   const int co_base = blockIdx.y * BN;
   const int nchunks = p.cin / TC_TK;
   const uint32_t kfull = p.K >= 32 ? 0xffffffffu : ((1u << p.K) - 1u);
-  const uint32_t mask = p.tapmask ? (p.tapmask[blockIdx.x] & kfull) : kfull;
+  const uint32_t mask = p.tapmask ? (p.tapmask[tile] & kfull) : kfull;
   const int nact = __popc(mask);
   const int nsteps = nact * nchunks;
   constexpr uint32_t TMEM_COLS = BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256));
@@ -649,7 +652,7 @@ int conv_tf32(const pcc_conv_args* a, cudaStream_t st) {
   TcParams p;
   p.in = a->in; p.weight_t = a->weight_t; p.bias = a->bias; p.nbr = a->nbr; p.tapmask = a->tapmask;
   p.film = a->film; p.film_rows = a->film_rows; p.residual = a->residual; p.res_rows = a->res_rows;
-  p.order = a->order; p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
+  p.order = a->order; p.tile_order = a->tile_order; p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
   p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope; p.flags = a->flags;
   if (use_tma() && a->n_in > 0) {
     if (a->cout > 64) return launch_tma<128>(p, a->n_in, st);

@@ -92,11 +92,11 @@ class KernelMap:
     [n_groups * ceil(n_out/128)] uint32 (as int32), order [n_groups, n_out] int32: tile row -> output
     row (None = identity).  n_groups > 1: the K offsets are cut into consecutive ranges, each with its
     own tile-row permutation (include/pcc_b200.h, pcc_kernel_map)."""
-    __slots__ = ("nbr", "tapmask", "K", "n_out", "stride", "order", "n_groups", "_pairs_cache")
+    __slots__ = ("nbr", "tapmask", "K", "n_out", "stride", "order", "n_groups", "tile_order", "_pairs_cache")
 
-    def __init__(self, nbr, tapmask, K, n_out, stride, order=None, n_groups=1):
+    def __init__(self, nbr, tapmask, K, n_out, stride, order=None, n_groups=1, tile_order=None):
         self.nbr, self.tapmask, self.K, self.n_out, self.stride = nbr, tapmask, K, n_out, stride
-        self.order, self.n_groups = order, n_groups
+        self.order, self.n_groups, self.tile_order = order, n_groups, tile_order
 
     def group_ranges(self):
         """[(k_lo, k_hi)] of the offset groups."""
@@ -217,7 +217,7 @@ class CoordMap:
         cap_g = ng if ng else AUTO_GROUPS
         tiles = max((n_out + TILE_M - 1) // TILE_M, 1)
         tapmask = torch.empty(cap_g * tiles, dtype=torch.int32, device=self.device)
-        order = None
+        order = tile_order = None
         if n_out:
             tk, tv, cap = self.hash()
             step = -out_map.ts if transpose else self.ts
@@ -227,21 +227,22 @@ class CoordMap:
                 ng = 1
             else:
                 order = torch.empty(cap_g * n_out, dtype=torch.int32, device=self.device)
+                tile_order = torch.empty(cap_g * tiles, dtype=torch.int32, device=self.device)
                 wsb = _L().pcc_kernel_map_ws_bytes(n_out)
                 ws = _ws(wsb, self.device)
             used = ctypes.c_int32(1)
             check(_L().pcc_kernel_map(_ptr(tk), _ptr(tv), cap, _ptr(out_map.keys), n_out, kernel_size, step,
-                                      align, _ptr(nbr), stride, _ptr(tapmask), _ptr(order), seg, ng,
+                                      align, _ptr(nbr), stride, _ptr(tapmask), _ptr(order), _ptr(tile_order), seg, ng,
                                       ctypes.byref(used), _ptr(ws), wsb, _stream()), "pcc_kernel_map")
             if ng == 0:
                 _count(6)
             ng = used.value
             if order is not None:
-                order, tapmask = order[:ng * n_out], tapmask[:ng * tiles]
-            _count(1 if order is None else 1 + 6 * ng)
+                order, tapmask, tile_order = order[:ng * n_out], tapmask[:ng * tiles], tile_order[:ng * tiles]
+            _count(1 if order is None else 1 + 7 * ng)
         else:
             ng = 1
-        kmap = KernelMap(nbr, tapmask, K, n_out, stride, order, ng)
+        kmap = KernelMap(nbr, tapmask, K, n_out, stride, order, ng, tile_order)
         # weak reference: out_map is often this map itself (stride-1 layers) or a map that caches the
         # transposed direction back to this one; a strong reference would make the pair collectable
         # only by the cycle collector and keep its kernel maps (K x n_out x 4 bytes) alive until then
@@ -270,7 +271,7 @@ def tile_segment_rows():
 
 
 # Offset groups of the kernel maps (pcc_kernel_map n_groups).  None = by mode: the exact path lets the
-# library measure each 27-offset map (n_groups = 0): maps whose mask-sorted tiles use >= 85 % of
+# library measure each 27-offset map (n_groups = 0): maps whose mask-sorted tiles use >= 72 % of
 # their MACs keep one group, ragged ones (e.g. the decoder's pruned sets under random-init weights,
 # 40-60 %) are cut into 3 groups of 9 offsets, each with its own mask-sorted tile rows (80-98 %), for
 # two extra launches per convolution.  The tensor-core kernel takes single-group maps only.
@@ -451,6 +452,9 @@ def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None
     a.flags = CONV_ROUND_OUT_TF32 if round_out else 0
     a.order = None if kmap.order is None else kmap.order.data_ptr()
     a.n_groups = kmap.n_groups
+    # longest-tiles-first launch order: only for the FP32-pipe-bound exact kernels; the tensor-core
+    # kernel is gather-bound and wants neighbouring tiles (an L2-sized window of the map) in flight together
+    a.tile_order = kmap.tile_order.data_ptr() if (kmap.tile_order is not None and mode == MODE_EXACT) else None
     if mode == MODE_TF32 and kmap.n_groups > 1:
         raise _lib.PccError("the tensor-core mode takes single-group kernel maps: build the map in tf32 mode "
                             "or with set_tap_groups(1)")

@@ -30,7 +30,7 @@ def test_conv_args_struct_layout(pcc):
     assert A.in_.offset == 0 and A.n_in.offset == 8 and A.cin.offset == 16 and A.cout.offset == 20
     assert A.weight.offset == 24 and A.nbr_stride.offset == 48 and A.K.offset == 64
     assert A.film.offset == 80 and A.out.offset == 112 and A.mode.offset == 136 and A.weight_t.offset == 144
-    assert A.order.offset == 152 and A.n_groups.offset == 160 and ctypes.sizeof(A) == 168
+    assert A.order.offset == 152 and A.n_groups.offset == 160 and A.tile_order.offset == 168 and ctypes.sizeof(A) == 176
 
 
 def test_product_does_not_import_oracle():

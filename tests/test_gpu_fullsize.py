@@ -74,7 +74,7 @@ def test_kernel_map_properties_full_size(pcc, level0):
     tiles = (n + 127) // 128
     pad = torch.full((27, tiles * 128 - n), -1, dtype=torch.int32, device=DEV)
     active = (torch.cat([km.nbr[:, :n], pad], 1).view(27, tiles, 128) >= 0).any(dim=2)
-    assert km.n_groups == 1                                             # a surface: mask-sorted tiles are >= 85 % useful
+    assert km.n_groups == 1                                             # a surface: mask-sorted tiles are >= 72 % useful
     for g, (lo, hi) in enumerate(km.group_ranges()):
         assert torch.equal(torch.sort(km.order.view(km.n_groups, -1)[g].long()).values, torch.arange(n, device=DEV))
         tm = km.tapmask.view(km.n_groups, -1)[g].long()

@@ -125,6 +125,11 @@ def test_kernel_map_conv(pcc, oracle, ks, groups, n, extent, ts):
                 if (tiled[k - lo, t * 128:(t + 1) * 128] >= 0).any():
                     want |= 1 << k
             assert tm[g * tiles + t] == want
+        if km.tile_order is not None:  # launch order: a permutation of the tiles, most active offsets first
+            to = km.tile_order.view(km.n_groups, -1)[g].cpu().numpy()
+            assert np.array_equal(np.sort(to), np.arange(tiles))
+            pc = np.array([bin(int(v)).count("1") for v in tm[g * tiles:(g + 1) * tiles]])[to]
+            assert np.all(pc[1:] <= pc[:-1])
     # stride 2
     s = m.stride2()
     km2 = m.kernel_map(s, ks)
