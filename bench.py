@@ -500,7 +500,7 @@ def run_ours(args, rank, world, local_rank):
     # ---- max over ranks
     # one frame at a time (no pipelining): the codec's latency, for reference
     lat = []
-    for _ in range(2):
+    for _ in range(3):
         torch.cuda.synchronize()
         tw = time.perf_counter()
         s_, sh_, k_, c_ = model.compress(*dev_inputs[0])
