@@ -95,6 +95,20 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar) : "memory");
 }
+// commit that arrives on the barrier at the same CTA-relative offset in every CTA of `mask`
+__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n" ::"r"(bar),
+               "h"(mask)
+               : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
 __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                           uint32_t accumulate) {
   asm volatile(
@@ -137,6 +151,15 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* desc, uint
       : "memory");
 }
 
+// tiled 2-D load delivered to the same CTA-relative address (and signalled on the same CTA-relative
+// barrier) in every CTA of `mask`
+__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const void* desc, uint32_t bar, int c0, int c1, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster"
+      " [%0], [%1, {%3, %4}], [%2], %5;\n" ::"r"(dst), "l"(desc), "r"(bar), "r"(c0), "r"(c1), "h"(mask)
+      : "memory");
+}
+
 // K-major, SWIZZLE_128B shared-memory matrix descriptor (sm_100 encoding):
 //   [0,14) start address >> 4, [16,30) leading byte offset >> 4 (unused for swizzled K-major),
 //   [32,46) stride byte offset >> 4 (1024 B between 8-row atoms), [46,48) version = 1,
@@ -171,7 +194,10 @@ struct TcSmem {
   static constexpr int TOTAL = NBR_OFFSET + 27 * TC_TM * 4 + 1024;  // + alignment slack
 };
 
-template <int BN>
+// CL = 2: the CTAs 2c and 2c + 1 (row tiles 2c, 2c + 1) form a cluster and walk the union of their
+// offsets in lockstep; each loads one half of every weight tile and multicasts it to both, so the
+// weight traffic out of L2 halves.  A stage is refilled only after BOTH CTAs' MMAs released it.
+template <int BN, int CL>
 __global__ void __launch_bounds__(TC_THREADS, 2)
 conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
   extern __shared__ unsigned char smem_raw[];
@@ -189,19 +215,28 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
-  const unsigned tile = p.tile_order ? (unsigned)__ldg(p.tile_order + blockIdx.x) : blockIdx.x;
+  const unsigned tile = (CL == 1 && p.tile_order) ? (unsigned)__ldg(p.tile_order + blockIdx.x) : blockIdx.x;
   const int64_t tile_base = (int64_t)tile * TC_TM;
   const int co_base = blockIdx.y * BN;
   const int nchunks = p.cin / TC_TK;
   const uint32_t kfull = p.K >= 32 ? 0xffffffffu : ((1u << p.K) - 1u);
-  const uint32_t mask = p.tapmask ? (p.tapmask[tile] & kfull) : kfull;
+  const unsigned n_tiles = (unsigned)((p.n_out + TC_TM - 1) / TC_TM);
+  uint32_t mask = kfull;
+  if (p.tapmask) {
+    mask = tile < n_tiles ? (p.tapmask[tile] & kfull) : 0u;
+    if (CL == 2) {
+      const unsigned other = tile ^ 1u;
+      if (other < n_tiles) mask |= p.tapmask[other] & kfull;
+    }
+  }
+  const uint32_t crank = CL == 2 ? cluster_ctarank() : 0u;
   const int nsteps = __popc(mask) * nchunks;
   constexpr uint32_t TMEM_COLS = BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256));
 
   if (tid == 0) {
     for (int s = 0; s < TC_STAGES; ++s) {
       mbar_init(full_bar(s), TC_PRODUCERS + 1);  // 128 gather arrivals + the weight tile's expect_tx
-      mbar_init(empty_bar(s), 1);
+      mbar_init(empty_bar(s), CL);               // one commit per CTA of the cluster
     }
     mbar_init(accum_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
@@ -223,6 +258,7 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
   }
   tc_fence_before();
   __syncthreads();
+  if (CL == 2) cluster_sync_all();  // the partner's barriers exist before anything is sent to them
   tc_fence_after();
   const uint32_t tmem_acc = *tmem_slot_ptr;
 
@@ -264,7 +300,11 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
       // weight slice Wt[pk][co_base .. +BN][ci chunk]: one tiled TMA load (SWIZZLE_128B box) by one thread
       if (tid == 0) {
         mbar_expect_tx(full_bar(stage), (uint32_t)S::B_BYTES);
-        tma_load_2d(b_stage, &tm_b, full_bar(stage), pchunk * TC_TK, pk * p.cout + co_base);
+        if (CL == 2)  // this CTA's half of the weight rows, to both CTAs
+          tma_load_2d_mc(b_stage + crank * (S::B_BYTES / 2), &tm_b, full_bar(stage), pchunk * TC_TK,
+                         pk * p.cout + co_base + (int)crank * (BN / 2), (uint16_t)3);
+        else
+          tma_load_2d(b_stage, &tm_b, full_bar(stage), pchunk * TC_TK, pk * p.cout + co_base);
       }
       tc_cp_commit();
       if (s >= TC_LAG) {
@@ -300,7 +340,10 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
           const uint64_t db = make_sw128_desc(b_stage + kk * 32);
           umma_tf32(tmem_acc, da, db, idesc, (s > 0 || kk > 0) ? 1u : 0u);
         }
-        umma_commit(empty_bar(stage));  // frees the smem stage when these MMAs retire
+        if (CL == 2)
+          umma_commit_mc(empty_bar(stage), (uint16_t)3);  // both CTAs' producers wait for both MMAs
+        else
+          umma_commit(empty_bar(stage));  // frees the smem stage when these MMAs retire
       }
       umma_commit(accum_bar);           // accumulator complete
     }
@@ -371,6 +414,7 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
   }
   tc_fence_before();
   __syncthreads();
+  if (CL == 2) cluster_sync_all();  // no CTA leaves while its partner may still send to it
   if (warp == 4) tmem_dealloc(tmem_acc, TMEM_COLS);
 }
 
@@ -411,17 +455,48 @@ static int make_map_2d(CUtensorMap* m, const float* ptr, int64_t rows, int64_t c
   return PCC_OK;
 }
 
+static int tf32_cluster() {
+  static int v = [] {
+    const char* e = getenv("PCC_TF32_CLUSTER");
+    return e ? atoi(e) : 0;
+  }();
+  return v;
+}
+
 template <int BN>
 static int launch_tc(const TcParams& p, cudaStream_t st) {
+  const size_t smem = TcSmem<BN>::TOTAL;
+  const unsigned tiles = (unsigned)ceil_div(p.n_out, TC_TM);
+  if (tf32_cluster() == 2 && BN >= 16) {
+    CUtensorMap tm_b;
+    const int rc = make_map_2d(&tm_b, p.weight_t, (int64_t)p.K * p.cout, p.cin, BN / 2);
+    if (rc) return rc;
+    static const cudaError_t attr =
+        cudaFuncSetAttribute(conv_tf32_kernel<BN, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    PCC_CHECK_CUDA(attr);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((tiles + 1u) & ~1u, (unsigned)ceil_div(p.cout, BN));
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    PCC_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_tf32_kernel<BN, 2>, tm_b, p));
+    return PCC_OK;
+  }
   CUtensorMap tm_b;
   const int rc = make_map_2d(&tm_b, p.weight_t, (int64_t)p.K * p.cout, p.cin, BN);
   if (rc) return rc;
-  const size_t smem = TcSmem<BN>::TOTAL;
   static const cudaError_t attr =
-      cudaFuncSetAttribute(conv_tf32_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaFuncSetAttribute(conv_tf32_kernel<BN, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   PCC_CHECK_CUDA(attr);
-  dim3 grid((unsigned)ceil_div(p.n_out, TC_TM), (unsigned)ceil_div(p.cout, BN));
-  conv_tf32_kernel<BN><<<grid, TC_THREADS, smem, st>>>(tm_b, p);
+  dim3 grid(tiles, (unsigned)ceil_div(p.cout, BN));
+  conv_tf32_kernel<BN, 1><<<grid, TC_THREADS, smem, st>>>(tm_b, p);
   PCC_CHECK_LAUNCH("conv_tf32_kernel");
   return PCC_OK;
 }
