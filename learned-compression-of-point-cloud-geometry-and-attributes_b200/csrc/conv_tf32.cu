@@ -184,12 +184,17 @@ __device__ __forceinline__ uint32_t sw128_offset(int row, int chunk) {
   return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) << 4));
 }
 
+// stages of the hybrid kernel by tile width: the narrower tiles have smaller stages, so a fourth one
+// still leaves room for 2 CTAs per SM — three stages in flight instead of two (the kernel is
+// latency-bound on bytes in flight)
 template <int BN>
 struct TcSmem {
+  static constexpr int STAGES = BN <= 64 ? 4 : TC_STAGES;
+  static constexpr int LAG = STAGES - 2;  // cp.async groups a producer thread keeps in flight
   static constexpr int A_BYTES = TC_TM * 128;
   static constexpr int B_BYTES = BN * 128;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int BAR_OFFSET = TC_STAGES * STAGE_BYTES;
+  static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
   static constexpr int NBR_OFFSET = BAR_OFFSET + 128;      // int32 [active taps <= 27][128 rows]
   static constexpr int TOTAL = NBR_OFFSET + 27 * TC_TM * 4 + 1024;  // + alignment slack
 };
@@ -206,12 +211,13 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
   const uint32_t base = (raw + 1023u) & ~1023u;
   unsigned char* sbase = smem_raw + (base - raw);
   using S = TcSmem<BN>;
+  constexpr int NST = S::STAGES, LAG = S::LAG;
   const uint32_t bar_base = base + S::BAR_OFFSET;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 8u * (TC_STAGES + s); };
-  const uint32_t accum_bar = bar_base + 8u * (2 * TC_STAGES);
-  const uint32_t tmem_slot = bar_base + 8u * (2 * TC_STAGES + 1);
-  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(sbase + S::BAR_OFFSET + 8 * (2 * TC_STAGES + 1));
+  auto empty_bar = [&](int s) { return bar_base + 8u * (NST + s); };
+  const uint32_t accum_bar = bar_base + 8u * (2 * NST);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * NST + 1);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(sbase + S::BAR_OFFSET + 8 * (2 * NST + 1));
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
@@ -234,7 +240,7 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
   constexpr uint32_t TMEM_COLS = BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256));
 
   if (tid == 0) {
-    for (int s = 0; s < TC_STAGES; ++s) {
+    for (int s = 0; s < NST; ++s) {
       mbar_init(full_bar(s), TC_PRODUCERS + 1);  // 128 gather arrivals + the weight tile's expect_tx
       mbar_init(empty_bar(s), CL);               // one commit per CTA of the cluster
     }
@@ -279,8 +285,8 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
     const char* in_b = reinterpret_cast<const char*>(p.in) + chunk * 16;
     const int64_t row_bytes = (int64_t)p.cin * 4;
     for (int s = 0; s < nsteps; ++s) {
-      const int stage = s % TC_STAGES;
-      if (s >= TC_STAGES) mbar_wait(empty_bar(stage), (uint32_t)(((s / TC_STAGES) - 1) & 1));
+      const int stage = s % NST;
+      if (s >= NST) mbar_wait(empty_bar(stage), (uint32_t)(((s / NST) - 1) & 1));
       if (need_idx) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -307,10 +313,10 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
           tma_load_2d(b_stage, &tm_b, full_bar(stage), pchunk * TC_TK, pk * p.cout + co_base);
       }
       tc_cp_commit();
-      if (s >= TC_LAG) {
-        tc_cp_wait<TC_LAG>();
+      if (s >= LAG) {
+        tc_cp_wait<LAG>();
         fence_proxy_async();
-        mbar_arrive(full_bar((s - TC_LAG) % TC_STAGES));
+        mbar_arrive(full_bar((s - LAG) % NST));
       }
       if (++pchunk == nchunks) {
         pchunk = 0;
@@ -323,14 +329,14 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
     // drain: publish the last min(LAG, nsteps) stages
     tc_cp_wait<0>();
     fence_proxy_async();
-    for (int s = (nsteps > TC_LAG ? nsteps - TC_LAG : 0); s < nsteps; ++s) mbar_arrive(full_bar(s % TC_STAGES));
+    for (int s = (nsteps > LAG ? nsteps - LAG : 0); s < nsteps; ++s) mbar_arrive(full_bar(s % NST));
   } else {
     // ============================ MMA issuer (one elected lane) ============================
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc_tf32(TC_TM, BN);
       for (int s = 0; s < nsteps; ++s) {
-        const int stage = s % TC_STAGES;
-        mbar_wait(full_bar(stage), (uint32_t)((s / TC_STAGES) & 1));
+        const int stage = s % NST;
+        mbar_wait(full_bar(stage), (uint32_t)((s / NST) & 1));
         tc_fence_after();
         const uint32_t a_stage = base + stage * S::STAGE_BYTES;
         const uint32_t b_stage = a_stage + S::A_BYTES;
