@@ -30,8 +30,13 @@ namespace pcc {
 constexpr int TC_TM = PCC_TILE_M;      // 128 rows = UMMA M
 constexpr int TC_TK = 32;              // fp32 channels per stage = 128 bytes = one swizzle row
 constexpr int TC_STAGES = 3;          // = TC_LAG + 2: one stage being consumed, one published, one landing
-constexpr int TC_PRODUCERS = 128;      // warps 0-3
-constexpr int TC_THREADS = 160;        // + warp 4 (MMA issuer, TMEM allocator)
+constexpr int TC_PWARPS = 8;           // producer warps.  tools/gather_bench.cu (profiles/r01_gather_microbench.txt):
+                                       // the shared-memory fill rate of gathered 128 B row chunks grows with the
+                                       // number of issuing threads, not with the groups in flight: 2 CTAs x 128
+                                       // threads x 8 copies reach 37-50 GB/s per SM, 2 x 256 x 4 reach 113
+constexpr int TC_PRODUCERS = 32 * TC_PWARPS;
+constexpr int TC_ROWS_PER_THREAD = TC_TM * 8 / TC_PRODUCERS;  // 16-byte copies per thread and stage
+constexpr int TC_THREADS = TC_PRODUCERS + 32;  // + the MMA-issue warp (also the TMEM allocator)
 constexpr int TC_LAG = 1;              // cp.async groups a producer thread keeps in flight
 // Two CTAs are resident per SM (3 x 32 KB stages + the tile's kernel-map rows each): one CTA's
 // epilogue and pipeline fill overlap the other's MMA stream.
@@ -241,13 +246,13 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
 
   if (tid == 0) {
     for (int s = 0; s < NST; ++s) {
-      mbar_init(full_bar(s), TC_PRODUCERS + 1);  // 128 gather arrivals + the weight tile's expect_tx
+      mbar_init(full_bar(s), TC_PRODUCERS + 1);  // the gather threads' arrivals + the weight tile's expect_tx
       mbar_init(empty_bar(s), CL);               // one commit per CTA of the cluster
     }
     mbar_init(accum_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
-  if (warp == 4) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == TC_PWARPS) tmem_alloc(tmem_slot, TMEM_COLS);
   // the tile's kernel-map rows for its active offsets, staged once (coalesced) so that gather
   // addresses never wait on a dependent global load
   int32_t* s_nbr = reinterpret_cast<int32_t*>(sbase + S::NBR_OFFSET);
@@ -268,18 +273,19 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
   tc_fence_after();
   const uint32_t tmem_acc = *tmem_slot_ptr;
 
-  if (warp < 4) {
+  if (warp < TC_PWARPS) {
     // ============================ producers: gather A rows, load B slice ============================
     const int chunk = tid & 7;   // 16-byte chunk inside the 128-byte row
-    const int rbase = tid >> 3;  // rows rbase + 16 j
+    constexpr int RSTEP = TC_PRODUCERS / 8;  // rows rbase + RSTEP j
     uint32_t pmask = mask;
     int pk = pmask ? (__ffs(pmask) - 1) : 0;
     int pa = 0;  // ordinal of pk among the active offsets
     int pchunk = 0;
     // per offset: source pointer of this thread's 16-byte chunk in each of its 8 rows (nullptr =
     // missing neighbour -> zero fill); per step only the channel-chunk displacement is added.
-    // Destination: rows rbase + 16 j share (row & 7), so the swizzled offset is off0 + 2048 j.
-    const char* rowp[8];
+    // Destination: rows rbase + RSTEP j share (row & 7), so the swizzled offset is off0 + 128 RSTEP j.
+    const int rbase = tid >> 3;
+    const char* rowp[TC_ROWS_PER_THREAD];
     bool need_idx = true;
     const uint32_t off0 = sw128_offset(rbase, chunk);
     const char* in_b = reinterpret_cast<const char*>(p.in) + chunk * 16;
@@ -289,8 +295,8 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
       if (s >= NST) mbar_wait(empty_bar(stage), (uint32_t)(((s / NST) - 1) & 1));
       if (need_idx) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int ix = s_nbr[pa * TC_TM + rbase + 16 * j];
+        for (int j = 0; j < TC_ROWS_PER_THREAD; ++j) {
+          const int ix = s_nbr[pa * TC_TM + rbase + RSTEP * j];
           rowp[j] = ix >= 0 ? in_b + ix * row_bytes : nullptr;
         }
         need_idx = false;
@@ -299,9 +305,9 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
       const uint32_t b_stage = a_stage + S::A_BYTES;
       const int cdisp = pchunk * (TC_TK * 4);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
+      for (int j = 0; j < TC_ROWS_PER_THREAD; ++j) {
         const bool ok = rowp[j] != nullptr;
-        tc_cp_async16(a_stage + off0 + 2048u * j, ok ? rowp[j] + cdisp : reinterpret_cast<const char*>(p.in), ok ? 16 : 0);
+        tc_cp_async16(a_stage + off0 + (uint32_t)(128 * RSTEP) * j, ok ? rowp[j] + cdisp : reinterpret_cast<const char*>(p.in), ok ? 16 : 0);
       }
       // weight slice Wt[pk][co_base .. +BN][ci chunk]: one tiled TMA load (SWIZZLE_128B box) by one thread
       if (tid == 0) {
@@ -356,13 +362,17 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
     __syncwarp();
   }
 
-  // ============================ epilogue (warps 0-3 own TMEM lanes 32w .. 32w+31) ============================
-  if (warp < 4) {
+  // ============================ epilogue ============================
+  // warp w reads TMEM lanes 32 (w % 4) .. + 31 (the hardware's lane quadrant of a warp); warps 0-3 take
+  // the first EPI_COLS columns, warps 4-7 the next, ...
+  constexpr int EPI_COLS = (BN / (TC_PWARPS / 4)) >= 32 ? BN / (TC_PWARPS / 4) : 32;  // columns per warp group
+  if (warp < TC_PWARPS && (warp >> 2) * EPI_COLS < BN) {
     if (nsteps > 0) {
       mbar_wait(accum_bar, 0);
       tc_fence_after();
     }
-    const int64_t t = tile_base + warp * 32 + lane;  // tile row -> output row
+    const int quad = warp & 3;
+    const int64_t t = tile_base + quad * 32 + lane;  // tile row -> output row
     const bool live = t < p.n_out;
     const int64_t o = (live && p.order) ? (int64_t)__ldg(p.order + t) : t;
     int64_t frow = o, rrow = o;
@@ -370,11 +380,11 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
     if (live && p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
     const bool vec4 = (p.out_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
 #pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 32) {
+    for (int c0 = (warp >> 2) * EPI_COLS; c0 < ((warp >> 2) + 1) * EPI_COLS && c0 < BN; c0 += 32) {
       if (co_base + c0 >= p.cout) break;  // warp-uniform
       uint32_t v[32];
       if (nsteps > 0) {
-        tmem_ld32(tmem_acc + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+        tmem_ld32(tmem_acc + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
       } else {
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = 0u;
@@ -421,7 +431,7 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
   tc_fence_before();
   __syncthreads();
   if (CL == 2) cluster_sync_all();  // no CTA leaves while its partner may still send to it
-  if (warp == 4) tmem_dealloc(tmem_acc, TMEM_COLS);
+  if (warp == TC_PWARPS) tmem_dealloc(tmem_acc, TMEM_COLS);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
