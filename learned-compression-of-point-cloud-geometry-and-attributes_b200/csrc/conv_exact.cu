@@ -79,10 +79,12 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int64_t o, in
   p.out[o * p.out_stride + col] = v;
 }
 
-template <int TN>
+// TK: input channels per stage (32; 4 for layers with cin <= 4, which would otherwise multiply 28
+// padded zeros per neighbour)
+template <int TN, int TK>
 struct ExactSmem {
-  float a[CE_STAGES][CE_TM][CE_APITCH];
-  float b[CE_STAGES][CE_TK][TN];
+  float a[CE_STAGES][CE_TM][TK + 4];
+  float b[CE_STAGES][TK][TN];
 };
 
 // VEC: cin % 4 == 0 && cout % 4 == 0 (16-byte cp.async sources are aligned)
@@ -100,7 +102,7 @@ __device__ __forceinline__ void ffma2(unsigned long long& d, unsigned long long 
   asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
 }
 
-template <int TN, bool VEC, int F2>
+template <int TN, bool VEC, int F2, int TK = CE_TK>
 __global__ void __launch_bounds__(CE_THREADS, 2)
 conv_exact_kernel(const ConvParams p) {
   constexpr int CN = TN / 16;  // output channels per thread
@@ -108,7 +110,7 @@ conv_exact_kernel(const ConvParams p) {
   constexpr bool PK = (F2 != 0) && (CN % 2 == 0);
   constexpr int CP = PK ? CN / 2 : 1;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  ExactSmem<TN>& sm = *reinterpret_cast<ExactSmem<TN>*>(smem_raw);
+  ExactSmem<TN, TK>& sm = *reinterpret_cast<ExactSmem<TN, TK>*>(smem_raw);
 
   const int tid = threadIdx.x;
   // compute mapping: warp w owns rows 32 (w >> 1) .. +31 and columns (TN / 2)(w & 1) .. ; inside the
@@ -123,7 +125,7 @@ conv_exact_kernel(const ConvParams p) {
   const unsigned tile = p.tile_order ? (unsigned)__ldg(p.tile_order + blockIdx.x) : blockIdx.x;
   const int64_t tile_base = (int64_t)tile * CE_TM;
   const int co_base = blockIdx.y * TN;
-  const int nchunks = (p.cin + CE_TK - 1) / CE_TK;
+  const int nchunks = (p.cin + TK - 1) / TK;
   const uint32_t mask = p.tapmask ? (p.tapmask[tile] & p.kbits) : p.kbits;
   const int nsteps = __popc(mask) * nchunks;
   if (nsteps == 0 && !p.first && !p.last) return;  // nothing to add to the partial sums of this tile
@@ -178,9 +180,9 @@ conv_exact_kernel(const ConvParams p) {
   }
 
   auto issue = [&](int stage) {
-    const int ci0 = pchunk * CE_TK;
-    // ---- A: 128 rows x 8 quads; thread -> quad q = tid & 7, rows (tid >> 3) + 32 j
-    {
+    const int ci0 = pchunk * TK;
+    // ---- A: 128 rows x TK / 4 quads; thread -> quad q = tid & 7, rows (tid >> 3) + 32 j
+    if ((tid & 7) < TK / 4) {
       const int q = tid & 7;
       const int ci = ci0 + q * 4;
 #pragma unroll
@@ -206,7 +208,7 @@ conv_exact_kernel(const ConvParams p) {
     // ---- B: TK rows x TN/4 quads
     {
       constexpr int QPR = TN / 4;                 // quads per weight row
-      constexpr int TOTAL = CE_TK * QPR;          // quads per stage
+      constexpr int TOTAL = TK * QPR;             // quads per stage
       const float* wk = p.weight + (int64_t)pk * p.cin * p.cout;
 #pragma unroll
       for (int t = tid; t < TOTAL; t += CE_THREADS) {
@@ -255,7 +257,7 @@ conv_exact_kernel(const ConvParams p) {
 
     const int st = s % CE_STAGES;
 #pragma unroll
-    for (int kv = 0; kv < CE_TK / AV; ++kv) {
+    for (int kv = 0; kv < TK / AV; ++kv) {
       float a[8][AV];
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -474,15 +476,15 @@ static int launch_head(const ConvParams& p, cudaStream_t st) {
   return PCC_OK;
 }
 
-template <int TN, bool VEC, int F2>
+template <int TN, bool VEC, int F2, int TK = CE_TK>
 static int launch_exact_v(const ConvParams& p, cudaStream_t st) {
-  const size_t smem = sizeof(ExactSmem<TN>);
+  const size_t smem = sizeof(ExactSmem<TN, TK>);
   dim3 grid((unsigned)ceil_div(p.n_out, CE_TM), (unsigned)ceil_div(p.cout, TN));
   // once per instantiation and process (thread-safe static init): keeps driver calls off the launch path
-  static const cudaError_t attr = cudaFuncSetAttribute(conv_exact_kernel<TN, VEC, F2>,
+  static const cudaError_t attr = cudaFuncSetAttribute(conv_exact_kernel<TN, VEC, F2, TK>,
                                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   PCC_CHECK_CUDA(attr);
-  conv_exact_kernel<TN, VEC, F2><<<grid, CE_THREADS, smem, st>>>(p);
+  conv_exact_kernel<TN, VEC, F2, TK><<<grid, CE_THREADS, smem, st>>>(p);
   PCC_CHECK_LAUNCH("conv_exact_kernel");
   return PCC_OK;
 }
@@ -501,6 +503,8 @@ static int launch_exact(const ConvParams& p, cudaStream_t st) {
                    ((reinterpret_cast<uintptr_t>(p.in) & 15) == 0) &&
                    ((reinterpret_cast<uintptr_t>(p.weight) & 15) == 0);
   const int f2 = exact_f2();
+  if (p.cin <= 4 && f2 != 0)  // thin input (the Q branch, the xyz/rgb input layer): 4-channel stages
+    return vec ? launch_exact_v<TN, true, 1, 4>(p, st) : launch_exact_v<TN, false, 1, 4>(p, st);
   if (f2 != 0) return vec ? launch_exact_v<TN, true, 1>(p, st) : launch_exact_v<TN, false, 1>(p, st);
   return vec ? launch_exact_v<TN, true, 0>(p, st) : launch_exact_v<TN, false, 0>(p, st);
 }
