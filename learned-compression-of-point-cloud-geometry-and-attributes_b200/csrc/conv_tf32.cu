@@ -76,6 +76,10 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.shared::cta.b64 st, [%0];\n}\n" ::"r"(bar) : "memory");
 }
+// the barrier receives this thread's arrival when all of its earlier cp.async copies have landed
+__device__ __forceinline__ void cp_async_arrive_noinc(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];\n" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n"
@@ -318,12 +322,9 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
         else
           tma_load_2d(b_stage, &tm_b, full_bar(stage), pchunk * TC_TK, pk * p.cout + co_base);
       }
-      tc_cp_commit();
-      if (s >= LAG) {
-        tc_cp_wait<LAG>();
-        fence_proxy_async();
-        mbar_arrive(full_bar((s - LAG) % NST));
-      }
+      // asynchronous publish: no thread waits for its copies; the stage's barrier completes when the
+      // last copy of the last thread (and the weight tile) has landed
+      cp_async_arrive_noinc(full_bar(stage));
       if (++pchunk == nchunks) {
         pchunk = 0;
         pmask &= pmask - 1;
@@ -332,10 +333,8 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
         need_idx = true;
       }
     }
-    // drain: publish the last min(LAG, nsteps) stages
-    tc_cp_wait<0>();
-    fence_proxy_async();
-    for (int s = (nsteps > LAG ? nsteps - LAG : 0); s < nsteps; ++s) mbar_arrive(full_bar(s % NST));
+    tc_cp_commit();
+    tc_cp_wait<0>();  // nothing of this CTA's copies is in flight when the epilogue starts
   } else {
     // ============================ MMA issuer (one elected lane) ============================
     if (lane == 0) {
@@ -343,6 +342,7 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
       for (int s = 0; s < nsteps; ++s) {
         const int stage = s % NST;
         mbar_wait(full_bar(stage), (uint32_t)((s / NST) & 1));
+        fence_proxy_async();  // the gathered rows were written through the generic proxy (cp.async)
         tc_fence_after();
         const uint32_t a_stage = base + stage * S::STAGE_BYTES;
         const uint32_t b_stage = a_stage + S::A_BYTES;
