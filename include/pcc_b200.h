@@ -227,6 +227,50 @@ int pcc_eb_likelihood(const float* z, const float* medians, const float* eb_para
 int pcc_color_finalize(const uint64_t* keys, const float* feats, int64_t n, int32_t c, float* out,
                        void* stream);
 
+/* ------------------------------------------------------------------ training path
+ * ColorModel.forward (model/model.py:51-93) under autograd, loss.backward() (train.py:189-203).
+ * Replaces ME's ConvolutionBackward / ConvolutionTransposeBackward and the autograd graph of
+ * CompressAI's GaussianConditional.forward(training=True).
+ *
+ * Data gradient: d in = conv(d out) over the REVERSED kernel map (pcc_kernel_map from the output
+ * side: transposed probe for a forward convolution and vice versa) with pcc_weight_transpose'd
+ * weights — pcc_conv_fwd, no extra entry point.
+ * Weight gradient: dweight[k][ci][co] = sum_j in[nbr[k][j]][ci] * gout[order[j]][co] over the
+ * forward kernel map (same nbr / tapmask / order / n_groups as pcc_conv_fwd took).  Deterministic:
+ * partial sums of fixed row ranges are added in a fixed order.  ws: pcc_conv_wgrad_ws_bytes(). */
+typedef struct pcc_wgrad_args {
+  const float* in;          /* [dev, n_in x cin] forward input */
+  const float* gout;        /* [dev, n_out x cout] gradient of the convolution's output (before bias) */
+  int32_t cin;
+  int32_t cout;
+  const int32_t* nbr;       /* [dev, K x nbr_stride] */
+  int64_t nbr_stride;
+  const uint32_t* tapmask;  /* [dev, n_groups x ceil(n_out / PCC_TILE_M)] or NULL */
+  const int32_t* order;     /* [dev, n_groups x n_out] or NULL */
+  int64_t n_out;
+  int32_t K;
+  int32_t n_groups;
+  float* dweight;           /* [dev, K x cin x cout] receives the gradient (overwritten) */
+  void* ws;
+  size_t ws_bytes;
+} pcc_wgrad_args;
+size_t pcc_conv_wgrad_ws_bytes(int32_t K, int32_t cin, int32_t cout);
+int pcc_conv_wgrad(const pcc_wgrad_args* args, void* stream);
+/* Backward of pcc_gather_rows: out[rows[i]] += g[i] (rows[i] < 0 skipped; NULL = identity). */
+int pcc_scatter_rows_add(const float* g, int32_t c, const int32_t* rows, int64_t n, float* out, void* stream);
+/* GaussianConditional.forward(training=True) (model/entropy_models.py:330 in train mode): y_noisy =
+ * y + U(-0.5, 0.5) is made by the caller; likelihood [n x c] row-major = max(Phi((0.5 - v) / s) -
+ * Phi((-0.5 - v) / s), likelihood_bound), v = |y_noisy - mean|, s = max(scale, scale_bound).  The
+ * backward recomputes it and applies CompressAI LowerBound's gradient rule to both bounds;
+ * g_param_rows [n x 2c] is the gradient of the GATHERED parameter rows (scatter it with
+ * pcc_scatter_rows_add). */
+int pcc_gc_likelihood_train_fwd(const float* y_noisy, const float* params, const int32_t* rows, int64_t n,
+                                int32_t c, float scale_bound, float likelihood_bound, float* likelihood,
+                                void* stream);
+int pcc_gc_likelihood_train_bwd(const float* y_noisy, const float* params, const int32_t* rows, int64_t n,
+                                int32_t c, float scale_bound, float likelihood_bound, const float* g_likelihood,
+                                float* g_y, float* g_param_rows, void* stream);
+
 /* ------------------------------------------------------------------ coordinate side channel
  * Replaces ColorModel.gpcc_encode / gpcc_decode (model/model.py:318-358, 360-395): the reference
  * writes the stride-8 latent coordinates to an ASCII PLY, runs the G-PCC `tmc3` binary as a

@@ -32,6 +32,15 @@ class ConvArgs(ctypes.Structure):
     ]
 
 
+class WgradArgs(ctypes.Structure):
+    """struct pcc_wgrad_args (include/pcc_b200.h)."""
+    _fields_ = [
+        ("in_", P), ("gout", P), ("cin", I32), ("cout", I32), ("nbr", P), ("nbr_stride", I64),
+        ("tapmask", P), ("order", P), ("n_out", I64), ("K", I32), ("n_groups", I32),
+        ("dweight", P), ("ws", P), ("ws_bytes", SZ),
+    ]
+
+
 # name -> (restype, argtypes); every symbol include/pcc_b200.h declares
 SIGNATURES = {
     "pcc_version": (I32, []),
@@ -64,6 +73,11 @@ SIGNATURES = {
     "pcc_eb_dequantize": (I32, [P, P, I64, I32, P, P]),
     "pcc_eb_likelihood": (I32, [P, P, P, I64, I32, F32, P, P, P]),
     "pcc_color_finalize": (I32, [P, P, I64, I32, P, P]),
+    "pcc_conv_wgrad_ws_bytes": (SZ, [I32, I32, I32]),
+    "pcc_conv_wgrad": (I32, [P, P]),
+    "pcc_scatter_rows_add": (I32, [P, I32, P, I64, P, P]),
+    "pcc_gc_likelihood_train_fwd": (I32, [P, P, P, I64, I32, F32, F32, P, P]),
+    "pcc_gc_likelihood_train_bwd": (I32, [P, P, P, I64, I32, F32, F32, P, P, P, P]),
     "pcc_octree_ws_bytes": (SZ, [I64]),
     "pcc_octree_encode": (I32, [P, I64, I32, I32, P, I64, P, P, SZ, P]),
     "pcc_octree_decode": (I32, [P, I64, I32, I32, P, I64, P, P, SZ, P]),

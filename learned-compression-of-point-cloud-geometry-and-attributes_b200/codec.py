@@ -16,6 +16,7 @@ Each method cites the reference lines it follows.
 import torch
 import torch.nn as nn
 
+from . import autograd as AG
 from . import ops
 from . import me as ME
 from .compressai_compat import CompressionModel, EntropyBottleneck, GaussianConditional, Wait, drive
@@ -81,6 +82,10 @@ class ST:
 def apply_conv(x, layer, out_map=None, transpose=False, **epilogue):
     """One fused convolution: x (ST) -> ST on out_map (default: same map)."""
     out_map = x.m if out_map is None else out_map
+    if AG.wants_grad(x.F, layer.kernel, epilogue.get("film"), epilogue.get("residual")):
+        # training (model/model.py:51-93 under autograd): same operator, epilogue unfused
+        return ST(AG.sparse_conv(x.F, x.m, out_map, layer.kernel_size, layer.kernel, layer.bias,
+                                 transpose=transpose, **epilogue), out_map)
     if isinstance(x.m, SlabMap):  # one slab of a partitioned scene: owned rows computed, halo rows exchanged
         return ST(x.m.conv(x.F, out_map, layer, transpose, epilogue), out_map)
     kmap = x.m.kernel_map(out_map, layer.kernel_size, transpose=transpose)
@@ -92,6 +97,13 @@ def on_map(m, F):
     if isinstance(m, SlabMap) and F.shape[0] != m.n_local:
         return m.lift(F)
     return F
+
+
+def gather(F, rows, add=None):
+    """out[i] = F[rows[i]] (0 when rows[i] < 0) (+ add[i]); differentiable when a gradient is wanted."""
+    if AG.wants_grad(F, add):
+        return AG.gather(F, rows, add)
+    return ops.gather_rows(F, rows, add=add)
 
 
 def rows_of(src_map, dst_map):
@@ -201,6 +213,10 @@ class GenerativeUpBlock(nn.Module):
         t = apply_conv(x, self.occ_predict[0], act=RELU)
         if full:
             return apply_conv(t, self.occ_predict[2]).F
+        last = self.occ_predict[2]
+        if AG.wants_grad(t.F, last.kernel):  # only channel 0 reaches the loss (loss.py:170): same gradient
+            c = min(4, last.out_channels)
+            return AG.sparse_conv(t.F, x.m, x.m, 3, last.kernel[:, :, :c], last.bias[:, :c])
         w, b = self._occ_head()
         return ops.conv(t.F, x.m.kernel_map(x.m, 3), w, b)
 
@@ -233,7 +249,7 @@ class GenerativeUpBlock(nn.Module):
             up_map = cand.select(sel)
         else:
             up_map = ops.CoordMap(ops.take_keys(cand.keys, sel), cand.ts, True)  # predictions.C[mask] (:164)
-        x = ST(on_map(up_map, ops.gather_rows(x.F, sel)), up_map)               # _prune_coords (:101-128)
+        x = ST(on_map(up_map, gather(x.F, sel)), up_map)                        # _prune_coords (:101-128)
         if not self.dense and self.condition_ablation is None:
             x = seq3(x, self.conv_2)
         return x, ST(logits, cand), up_map
@@ -318,7 +334,7 @@ class AnalysisTransform(nn.Module):
         if self.cond_conv is not None:
             Q_plus = seq3(x, self.cond_conv)
             # Q.F + Q_plus.features_at_coordinates(Q.C)  (:94-98)
-            Q = ST(on_map(Q.m, ops.gather_rows(Q_plus.F, rows_of(x.m, Q.m), add=Q.F)), Q.m)
+            Q = ST(on_map(Q.m, gather(Q_plus.F, rows_of(x.m, Q.m), add=Q.F)), Q.m)
         Q, beta_gammas = self.condition_encoder(Q)
         x = apply_conv(x, self.pre_conv[0], act=RELU)
         x = apply_conv(x, self.down_1, out_map=x.m.stride2())
@@ -330,7 +346,7 @@ class AnalysisTransform(nn.Module):
         x = apply_conv(x, self.down_3, out_map=x.m.stride2())
         x = self.scale_3(x, beta_gammas[2])
         x = apply_conv(x, self.post_conv)
-        Q = ST(on_map(x.m, ops.gather_rows(Q.F, rows_of(Q.m, x.m))), x.m)  # (:123-125)
+        Q = ST(on_map(x.m, gather(Q.F, rows_of(Q.m, x.m))), x.m)  # (:123-125)
         k.reverse()
         return x, Q, k
 
@@ -369,7 +385,7 @@ class SparseSynthesisTransform(nn.Module):
         with stage("g_s.pre"):
             if self.cond_conv is not None:
                 Q_plus = seq3(x, self.cond_conv)
-                Q = ST(on_map(Q.m, ops.gather_rows(Q_plus.F, rows_of(x.m, Q.m), add=Q.F)), Q.m)  # (:258-265)
+                Q = ST(on_map(Q.m, gather(Q_plus.F, rows_of(x.m, Q.m), add=Q.F)), Q.m)  # (:258-265)
             x = apply_conv(x, self.pre_conv[0], act=RELU)
             Q = seq5(Q, self.q_pre_conv)
         predictions = []
@@ -445,7 +461,10 @@ class MeanScaleHyperprior_Map(CompressionModel):
         return apply_conv(q, self.h_q[6])
 
     def forward(self, y):
-        """Eval-mode forward with likelihoods (:309-337)."""
+        """Forward with likelihoods (:309-337); in training mode with CompressAI's additive-noise
+        quantisation and differentiable likelihoods."""
+        if self.training:
+            return self._forward_train(y)
         z = self.run_h_a(y)
         med, packed = self.entropy_bottleneck._device_params(z.F.device)
         z_hat_f, z_lik = ops.eb_likelihood(z.F, med, packed, 1e-9)
@@ -455,6 +474,16 @@ class MeanScaleHyperprior_Map(CompressionModel):
         gc = self.gaussian_conditional
         y_hat_f, y_lik = ops.gc_likelihood(y.F, params.F, None, gc._scale_bound, 1e-9)
         return ST(y_hat_f, y.m), Q_hat, (y_lik.unsqueeze(0), z_lik.unsqueeze(0))
+
+    def _forward_train(self, y):
+        z = self.run_h_a(y)
+        z_hat_cn, z_lik = self.entropy_bottleneck(z.F.t().unsqueeze(0), training=True)  # (:313)
+        z_hat = ST(z_hat_cn[0].t().contiguous(), z.m)
+        params = self.run_h_s(z_hat, at_map=y.m)       # gaussian_params at y.C (:324-327)
+        Q_hat = self.run_h_q(z_hat)
+        gc = self.gaussian_conditional
+        y_hat_f, y_lik = gc.forward_rows(y.F, params.F, training=True)  # (:330)
+        return ST(y_hat_f, y.m), Q_hat, (y_lik.t().unsqueeze(0), z_lik)
 
     def compress(self, y):
         return drive(self.compress_gen(y))
@@ -573,15 +602,42 @@ class ColorModel(CompressionModel):
         Qt = _canonical(qc, qf.to(dev, non_blocking=True), 1, share_with=inp.m)
         return inp, Qt
 
-    @torch.no_grad()
+    def _inputs_sparse(self, x, Q):
+        """model/model.py:58-66 for a (batched) SparseTensor-like x with .C [N,4] and .F [N,3]."""
+        dev = self.device
+        xc, xf = x.C.to(dev), x.F.to(dev)
+        feats = torch.cat([torch.ones((xc.shape[0], 1), device=dev), xf], dim=1)
+        inp = _canonical(xc.int(), feats, 1)
+        qc, qf = (Q if isinstance(Q, (tuple, list)) else (Q.C, Q.F))
+        qc = qc.to(dev)
+        if qc.is_floating_point():
+            qc = torch.floor(qc).int()
+        return inp, _canonical(qc, qf.to(dev), 1, share_with=inp.m)
+
     def forward(self, x, Q, Lambda=None):
-        """Eval-mode forward (model/model.py:51-93): likelihoods instead of strings."""
-        inp, Qt = self._inputs(x, Q) if torch.is_tensor(x) else (x, Q)
-        y, Qy, k = self.g_a(inp, Qt)
-        y_hat, Q_hat, lik = self.entropy_model(y)
-        x_hat, points, predictions = self.g_s(y_hat, Q_hat, coords=ST(None, inp.m), k=k, full_predictions=True)
-        return {"prediction": x_hat, "points": points, "occ_predictions": predictions, "q_map": Lambda,
-                "likelihoods": {"y": lik[0], "z": lik[1]}}
+        """model/model.py:51-93: likelihoods instead of strings.  x: [N,6] tensor (one cloud), a
+        SparseTensor-like (.C with batch ids, .F colours: train.py:176-183) or an internal ST.  In
+        training mode (``model.train()``) the pass is recorded for ``loss.backward()``; otherwise it
+        runs without a tape on the fused kernels."""
+        with torch.set_grad_enabled(self.training and torch.is_grad_enabled()):
+            if isinstance(x, ST):
+                inp, Qt = x, Q
+            elif torch.is_tensor(x):
+                inp, Qt = self._inputs(x, Q)
+            else:
+                inp, Qt = self._inputs_sparse(x, Q)
+            y, Qy, k = self.g_a(inp, Qt)
+            if self.entropy_model_map is None:
+                y_hat, Q_hat, lik = self.entropy_model(y)
+                likelihoods = {"y": lik[0], "z": lik[1]}
+            else:  # (:78-81)
+                y_hat, _, y_lik = self.entropy_model(y)
+                Q_hat, _, Q_lik = self.entropy_model_map(Qy)
+                likelihoods = {"y": [y_lik[0], Q_lik[0]], "z": [y_lik[1], Q_lik[1]]}
+            x_hat, points, predictions = self.g_s(y_hat, Q_hat, coords=ST(None, inp.m), k=k,
+                                                  full_predictions=not self.training)
+            return {"prediction": x_hat, "points": points, "occ_predictions": predictions, "q_map": Lambda,
+                    "likelihoods": likelihoods, "input": inp}
 
     @torch.no_grad()
     def compress(self, x, Q, path=None):

@@ -34,15 +34,48 @@ def get_scale_table(min=0.11, max=256, levels=64):
     return torch.exp(torch.linspace(math.log(min), math.log(max), levels))
 
 
+class _LowerBoundFn(torch.autograd.Function):
+    """compressai.ops.LowerBoundFunction: max(x, bound); the gradient passes where x >= bound or
+    where it would move x up (grad < 0)."""
+
+    @staticmethod
+    def forward(ctx, x, bound):
+        ctx.save_for_backward(x, bound)
+        return torch.max(x, bound)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, bound = ctx.saved_tensors
+        return ((x >= bound) | (g < 0)).to(g.dtype) * g, None
+
+
 class LowerBound(nn.Module):
-    """compressai.ops.LowerBound (forward only): max(x, bound); carries the ``bound`` buffer."""
+    """compressai.ops.LowerBound: max(x, bound) with the pass-through gradient rule; carries the
+    ``bound`` buffer."""
 
     def __init__(self, bound):
         super().__init__()
         self.register_buffer("bound", torch.Tensor([float(bound)]))
 
     def forward(self, x):
-        return torch.max(x, self.bound.to(x.device))
+        return _LowerBoundFn.apply(x, self.bound.to(x.device))
+
+
+# Additive quantisation noise of the training path (compressai EntropyModel.quantize, mode "noise":
+# inputs + U(-0.5, 0.5)).  Tests replace the source to feed the oracle and the product the same draw.
+_noise_source = None
+
+
+def set_noise_source(fn):
+    """fn(tensor) -> noise tensor of the same shape/device in [-0.5, 0.5); None restores torch's RNG."""
+    global _noise_source
+    _noise_source = fn
+
+
+def quantization_noise(like):
+    if _noise_source is not None:
+        return _noise_source(like).to(like.device, like.dtype)
+    return torch.empty_like(like).uniform_(-0.5, 0.5)
 
 
 # ------------------------------------------------------------------------------ asynchronous coder
@@ -277,11 +310,27 @@ class EntropyBottleneck(EntropyModel):
 
     def forward(self, x, training=None):
         if training if training is not None else self.training:
-            raise PccError("training-mode (noise) quantisation is outside the encode/decode path")
+            return self._forward_train(x)
         z = _rows_cn(x)
         med, packed = self._device_params(z.device)
         z_hat, lik = ops.eb_likelihood(z, med, packed, self._likelihood_bound if self.use_likelihood_bound else 0.0)
         return z_hat.t().unsqueeze(0), lik.unsqueeze(0)
+
+    def _forward_train(self, x):
+        """EntropyBottleneck.forward(training=True): x [1, C, N] -> (x + noise, likelihood), both
+        [1, C, N], on the autograd tape.  The factorised density is C x 58 parameters applied to
+        C x N values (N = 1.2 k per 800 k-point frame): plain tensor expressions."""
+        self._dev_cache.clear()  # parameters are about to change: eval-mode tables are stale
+        values = x.permute(1, 0, 2).reshape(self.channels, 1, -1)
+        outputs = values + quantization_noise(values)
+        lower = self._logits_cumulative(outputs - 0.5)
+        upper = self._logits_cumulative(outputs + 0.5)
+        sign = -torch.sign(lower + upper).detach()
+        lik = torch.abs(torch.sigmoid(sign * upper) - torch.sigmoid(sign * lower))
+        if self.use_likelihood_bound:
+            lik = self.likelihood_lower_bound(lik)
+        shape = (self.channels, x.shape[0], -1)
+        return outputs.reshape(shape).permute(1, 0, 2), lik.reshape(shape).permute(1, 0, 2)
 
     def quantize_rows(self, z):
         """z [N, C] -> (symbols [C, N] int32 device, z_hat [N, C])."""
@@ -375,9 +424,21 @@ class GaussianConditional(EntropyModel):
         idx = ops.gc_build_indexes(params, None, s.shape[0], s.shape[1], self._table_dev(s.device), self._scale_bound)
         return idx.unsqueeze(0)
 
+    def forward_rows(self, y, params, rows=None, training=None):
+        """Row-major form of forward: y [N, C], params [P, 2C] = scales | means, rows: latent row ->
+        params row.  -> (y_hat or y + noise [N, C], likelihood [N, C])."""
+        from . import autograd as AG
+        lb = self._likelihood_bound if self.use_likelihood_bound else 0.0
+        if training if training is not None else self.training:
+            y_noisy = y + quantization_noise(y)
+            return y_noisy, AG.gc_likelihood(y_noisy, params, rows, self._scale_bound, lb)
+        y_hat, lik = ops.gc_likelihood(y, params, rows, self._scale_bound, lb)
+        return y_hat, lik.t()
+
     def forward(self, inputs, scales, means=None, training=None):
         if training if training is not None else self.training:
-            raise PccError("training-mode (noise) quantisation is outside the encode/decode path")
+            y_noisy, lik = self.forward_rows(_rows_cn(inputs), self._params(scales, means), training=True)
+            return y_noisy.t().unsqueeze(0), lik.t().unsqueeze(0)
         y = _rows_cn(inputs)
         y_hat, lik = ops.gc_likelihood(y, self._params(scales, means), None, self._scale_bound,
                                        self._likelihood_bound if self.use_likelihood_bound else 0.0)

@@ -1,0 +1,354 @@
+// Training-path kernels (reference: ColorModel.forward model/model.py:51-93 with
+// loss.backward() in train.py:189-203).  The reference gets these from MinkowskiEngine's
+// ConvolutionBackward (data + weight gradients) and torch autograd over CompressAI's modules.
+//
+//  * data gradient: no kernel here — din = conv(gout, reversed kernel map, W^T) runs on the forward
+//    kernels (pcc_conv_fwd) with the map built from the output side.
+//  * weight gradient (this file): dW[k] = sum over pairs of in[nbr[k][j]]^T (x) gout[order[j]], an
+//    (cin x rows) x (rows x cout) product per offset with both operands gathered.  Output-stationary in
+//    registers, cp.async double-buffered row stages, tiles without the offset skipped by the kernel
+//    map's tap masks.  The row range is cut into S splits whose partial sums are added in a fixed order
+//    by a second kernel, so the gradient is deterministic (no float atomics).
+//  * rows scatter-add (backward of pcc_gather_rows), Gaussian likelihood with noise-quantised inputs
+//    and its derivatives (CompressAI GaussianConditional.forward in training mode, LowerBound's
+//    gradient rule included).
+#include "pcc_common.cuh"
+
+#include <algorithm>
+
+namespace pcc {
+
+__device__ __forceinline__ void cpa16(void* smem, const void* gmem, bool valid) {
+  const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem);
+  const int bytes = valid ? 16 : 0;  // src-size 0 -> 16 zero bytes
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(gmem), "r"(bytes));
+}
+__device__ __forceinline__ void cpa_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cpa_wait() {
+  asm volatile("cp.async.wait_group %0;\n" ::"n"(N));
+}
+
+constexpr int WG_THREADS = 256;
+constexpr int WG_ROWS = 32;  // rows per stage
+
+struct WgradParams {
+  const float* in;
+  const float* gout;
+  const int32_t* nbr;       // this offset group's view: nbr + k * nbr_stride, tile-row indexed
+  const uint32_t* tapmask;  // group's masks or NULL
+  const int32_t* order;     // group's tile row -> output row or NULL
+  float* part;              // [S][K][cin][cout]
+  int64_t nbr_stride, n_out;
+  int cin, cout, K, k_lo, k_hi, S;
+};
+
+// CTA: one offset k, one (ci tile, co tile), row tiles s, s + S, ...  Thread (ty, tx) of a 16 x 16
+// arrangement owns TM x TN elements of the 16 TM x 16 TN tile.
+template <int TM, int TN, bool VEC>
+__global__ void __launch_bounds__(WG_THREADS)
+conv_wgrad_kernel(const WgradParams p) {
+  constexpr int CI_T = 16 * TM, CO_T = 16 * TN;
+  constexpr int STAGE = WG_ROWS * (CI_T + CO_T);
+  extern __shared__ __align__(16) float smem[];
+  __shared__ int32_t s_in[PCC_TILE_M], s_go[PCC_TILE_M];
+  const int k = p.k_lo + blockIdx.y;
+  const int co_tiles = (p.cout + CO_T - 1) / CO_T;
+  const int ci0 = (blockIdx.z / co_tiles) * CI_T, co0 = (blockIdx.z % co_tiles) * CO_T;
+  const int tid = threadIdx.x, ty = tid / 16, tx = tid % 16;
+  float acc[TM][TN];
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+
+  const int64_t tiles = (p.n_out + PCC_TILE_M - 1) / PCC_TILE_M;
+  for (int64_t tile = blockIdx.x; tile < tiles; tile += p.S) {
+    if (p.tapmask && !((p.tapmask[tile] >> k) & 1u)) continue;
+    __syncthreads();  // previous tile's readers of s_in / s_go and of the stages are done
+    if (tid < PCC_TILE_M) {
+      const int64_t t = tile * PCC_TILE_M + tid;
+      int32_t ri = -1, ro = -1;
+      if (t < p.n_out) {
+        ri = __ldg(p.nbr + (int64_t)k * p.nbr_stride + t);
+        ro = p.order ? __ldg(p.order + t) : (int32_t)t;
+      }
+      s_in[tid] = ri;
+      s_go[tid] = ri >= 0 ? ro : -1;
+    }
+    __syncthreads();
+    auto load_stage = [&](int chunk, int buf) {
+      float* a_s = smem + buf * STAGE;
+      float* g_s = a_s + WG_ROWS * CI_T;
+      if (VEC) {
+        for (int e = tid; e < WG_ROWS * (CI_T / 4); e += WG_THREADS) {
+          const int r = e / (CI_T / 4), c4 = e % (CI_T / 4);
+          const int32_t row = s_in[chunk * WG_ROWS + r];
+          const bool ok = row >= 0 && ci0 + c4 * 4 < p.cin;
+          cpa16(a_s + r * CI_T + c4 * 4, ok ? p.in + (int64_t)row * p.cin + ci0 + c4 * 4 : p.in, ok);
+        }
+        for (int e = tid; e < WG_ROWS * (CO_T / 4); e += WG_THREADS) {
+          const int r = e / (CO_T / 4), c4 = e % (CO_T / 4);
+          const int32_t row = s_go[chunk * WG_ROWS + r];
+          const bool ok = row >= 0 && co0 + c4 * 4 < p.cout;
+          cpa16(g_s + r * CO_T + c4 * 4, ok ? p.gout + (int64_t)row * p.cout + co0 + c4 * 4 : p.gout, ok);
+        }
+      } else {
+        for (int e = tid; e < WG_ROWS * CI_T; e += WG_THREADS) {
+          const int r = e / CI_T, c = e % CI_T;
+          const int32_t row = s_in[chunk * WG_ROWS + r];
+          a_s[e] = (row >= 0 && ci0 + c < p.cin) ? __ldg(p.in + (int64_t)row * p.cin + ci0 + c) : 0.f;
+        }
+        for (int e = tid; e < WG_ROWS * CO_T; e += WG_THREADS) {
+          const int r = e / CO_T, c = e % CO_T;
+          const int32_t row = s_go[chunk * WG_ROWS + r];
+          g_s[e] = (row >= 0 && co0 + c < p.cout) ? __ldg(p.gout + (int64_t)row * p.cout + co0 + c) : 0.f;
+        }
+      }
+      cpa_commit();
+    };
+    constexpr int CHUNKS = PCC_TILE_M / WG_ROWS;
+    load_stage(0, 0);
+#pragma unroll 1
+    for (int c = 0; c < CHUNKS; ++c) {
+      if (c + 1 < CHUNKS) {
+        load_stage(c + 1, (c + 1) & 1);
+        cpa_wait<1>();
+      } else {
+        cpa_wait<0>();
+      }
+      __syncthreads();
+      const float* a_s = smem + (c & 1) * STAGE;
+      const float* g_s = a_s + WG_ROWS * CI_T;
+#pragma unroll 4
+      for (int r = 0; r < WG_ROWS; ++r) {
+        float a[TM], b[TN];
+        if (TM % 4 == 0) {
+#pragma unroll
+          for (int i = 0; i < TM; i += 4)
+            *reinterpret_cast<float4*>(a + i) = *reinterpret_cast<const float4*>(a_s + r * CI_T + ty * TM + i);
+        } else {
+#pragma unroll
+          for (int i = 0; i < TM; ++i) a[i] = a_s[r * CI_T + ty * TM + i];
+        }
+        if (TN % 4 == 0) {
+#pragma unroll
+          for (int j = 0; j < TN; j += 4)
+            *reinterpret_cast<float4*>(b + j) = *reinterpret_cast<const float4*>(g_s + r * CO_T + tx * TN + j);
+        } else {
+#pragma unroll
+          for (int j = 0; j < TN; ++j) b[j] = g_s[r * CO_T + tx * TN + j];
+        }
+#pragma unroll
+        for (int i = 0; i < TM; ++i)
+#pragma unroll
+          for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+      }
+      __syncthreads();  // stage (c & 1) is overwritten by the load issued in the next iteration
+    }
+  }
+  float* dst = p.part + ((int64_t)blockIdx.x * p.K + k) * p.cin * p.cout;
+#pragma unroll
+  for (int i = 0; i < TM; ++i) {
+    const int ci = ci0 + ty * TM + i;
+    if (ci >= p.cin) continue;
+#pragma unroll
+    for (int j = 0; j < TN; ++j) {
+      const int co = co0 + tx * TN + j;
+      if (co < p.cout) dst[(int64_t)ci * p.cout + co] = acc[i][j];
+    }
+  }
+}
+
+__global__ void wgrad_reduce_kernel(const float* __restrict__ part, int S, int64_t n, float* __restrict__ dw) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float s = 0.f;
+  for (int j = 0; j < S; ++j) s = __fadd_rn(s, __ldg(part + (int64_t)j * n + i));
+  dw[i] = s;
+}
+
+static int wgrad_splits(int K, int zt) {
+  // about four CTAs per SM over (splits x offsets x channel tiles)
+  const int target = 4 * sm_count();
+  int s = target / std::max(1, K * zt);
+  return std::max(1, std::min(s, 64));
+}
+
+template <int TM, int TN, bool VEC>
+static int launch_wgrad(const WgradParams& p, int zt, cudaStream_t st) {
+  constexpr size_t smem = 2 * WG_ROWS * (16 * TM + 16 * TN) * sizeof(float);
+  static bool attr_done = false;
+  if (!attr_done) {
+    PCC_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<TM, TN, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_done = true;
+  }
+  dim3 grid((unsigned)p.S, (unsigned)(p.k_hi - p.k_lo), (unsigned)zt);
+  conv_wgrad_kernel<TM, TN, VEC><<<grid, WG_THREADS, smem, st>>>(p);
+  PCC_CHECK_LAUNCH("conv_wgrad_kernel");
+  return PCC_OK;
+}
+
+static int tile_for(int c) { return c > 64 ? 8 : c > 16 ? 4 : 1; }
+
+// ---------------------------------------------------------------- scatter-add of rows
+__global__ void scatter_rows_add_kernel(const float* __restrict__ g, int c, const int32_t* __restrict__ rows,
+                                        int64_t n, float* __restrict__ out) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * c) return;
+  const int64_t i = t / c;
+  const int j = (int)(t % c);
+  const int32_t r = rows ? __ldg(rows + i) : (int32_t)i;
+  if (r >= 0) atomicAdd(out + (int64_t)r * c + j, __ldg(g + t));
+}
+
+// ---------------------------------------------------------------- Gaussian likelihood, training mode
+__device__ __forceinline__ float std_cdf(float x) { return 0.5f * erfcf(-0.70710678118654752440f * x); }
+__device__ __forceinline__ float std_pdf(float x) { return 0.3989422804014327f * __expf(-0.5f * x * x); }
+
+// lik[i][ch] = max(Phi((0.5 - v) / s) - Phi((-0.5 - v) / s), bound), v = |y~ - mean|, s = max(scale, sb)
+__global__ void gc_train_fwd_kernel(const float* __restrict__ yt, const float* __restrict__ params,
+                                    const int32_t* __restrict__ rows, int64_t n, int c, float sb, float lb,
+                                    float* __restrict__ lik) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * c) return;
+  const int64_t i = t / c;
+  const int ch = (int)(t % c);
+  const int32_t pr = rows ? __ldg(rows + i) : (int32_t)i;
+  float scale = 0.f, mean = 0.f;
+  if (pr >= 0) {
+    scale = __ldg(params + (int64_t)pr * 2 * c + ch);
+    mean = __ldg(params + (int64_t)pr * 2 * c + c + ch);
+  }
+  const float s = fmaxf(scale, sb);
+  const float v = fabsf(__ldg(yt + t) - mean);
+  const float l = std_cdf((0.5f - v) / s) - std_cdf((-0.5f - v) / s);
+  lik[t] = fmaxf(l, lb);
+}
+
+// g_lik -> g_y [n, c] and g_prow [n, 2c] (d/d scale | d/d mean of the gathered parameter row).
+// LowerBound backward (compressai.ops.LowerBound): the gradient passes when x >= bound or it is negative.
+__global__ void gc_train_bwd_kernel(const float* __restrict__ yt, const float* __restrict__ params,
+                                    const int32_t* __restrict__ rows, int64_t n, int c, float sb, float lb,
+                                    const float* __restrict__ g_lik, float* __restrict__ g_y,
+                                    float* __restrict__ g_prow) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * c) return;
+  const int64_t i = t / c;
+  const int ch = (int)(t % c);
+  const int32_t pr = rows ? __ldg(rows + i) : (int32_t)i;
+  float scale = 0.f, mean = 0.f;
+  if (pr >= 0) {
+    scale = __ldg(params + (int64_t)pr * 2 * c + ch);
+    mean = __ldg(params + (int64_t)pr * 2 * c + c + ch);
+  }
+  const float s = fmaxf(scale, sb);
+  const float d = __ldg(yt + t) - mean;
+  const float v = fabsf(d);
+  const float u = (0.5f - v) / s, w = (-0.5f - v) / s;
+  const float l = std_cdf(u) - std_cdf(w);
+  float g = __ldg(g_lik + t);
+  if (!(l >= lb || g < 0.f)) g = 0.f;
+  const float pu = std_pdf(u), pw = std_pdf(w);
+  const float dl_dv = (pw - pu) / s;
+  const float sgn = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);  // torch.abs' subgradient
+  const float gy = g * dl_dv * sgn;
+  float gs = g * (w * pw - u * pu) / s;
+  if (!(scale >= sb || gs < 0.f)) gs = 0.f;
+  g_y[t] = gy;
+  g_prow[i * 2 * c + ch] = gs;
+  g_prow[i * 2 * c + c + ch] = -gy;
+}
+
+}  // namespace pcc
+
+using namespace pcc;
+
+extern "C" {
+
+size_t pcc_conv_wgrad_ws_bytes(int32_t K, int32_t cin, int32_t cout) {
+  const int tm = tile_for(cin), tn = tile_for(cout);
+  const int zt = (int)(ceil_div(cin, 16 * tm) * ceil_div(cout, 16 * tn));
+  return (size_t)wgrad_splits(K, zt) * K * cin * cout * sizeof(float) + 256;
+}
+
+int pcc_conv_wgrad(const pcc_wgrad_args* a, void* stream) {
+  PCC_REQUIRE(a != nullptr, "null args");
+  PCC_REQUIRE(a->dweight && a->cin > 0 && a->cout > 0 && a->K > 0 && a->K <= 27, "bad shape");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t wn = (int64_t)a->K * a->cin * a->cout;
+  if (a->n_out == 0) {
+    PCC_CHECK_CUDA(cudaMemsetAsync(a->dweight, 0, wn * sizeof(float), st));
+    return PCC_OK;
+  }
+  PCC_REQUIRE(a->in && a->gout && a->nbr && a->ws, "null pointer");
+  PCC_REQUIRE(a->nbr_stride >= a->n_out, "nbr_stride < n_out");
+  PCC_REQUIRE(a->ws_bytes >= pcc_conv_wgrad_ws_bytes(a->K, a->cin, a->cout), "workspace too small");
+  PCC_REQUIRE(a->n_groups <= 1 || (a->order && a->n_groups <= a->K), "n_groups > 1 needs order and n_groups <= K");
+  const int tm = tile_for(a->cin), tn = tile_for(a->cout);
+  const int zt = (int)(ceil_div(a->cin, 16 * tm) * ceil_div(a->cout, 16 * tn));
+  WgradParams p;
+  p.in = a->in; p.gout = a->gout; p.nbr = a->nbr; p.part = reinterpret_cast<float*>(a->ws);
+  p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.cin = a->cin; p.cout = a->cout; p.K = a->K;
+  p.S = wgrad_splits(a->K, zt);
+  const bool vec = a->cin % 4 == 0 && a->cout % 4 == 0 && tm >= 4 && tn >= 4 &&
+                   (reinterpret_cast<uintptr_t>(a->in) & 15) == 0 && (reinterpret_cast<uintptr_t>(a->gout) & 15) == 0;
+  const int ng = a->n_groups > 1 ? a->n_groups : 1;
+  const int per = (a->K + ng - 1) / ng;
+  const int64_t tiles = ceil_div(a->n_out, PCC_TILE_M);
+  for (int g = 0; g < ng; ++g) {
+    p.k_lo = g * per;
+    p.k_hi = std::min((g + 1) * per, (int)a->K);
+    if (p.k_lo >= p.k_hi) break;
+    p.order = a->order ? a->order + (int64_t)g * a->n_out : nullptr;
+    p.tapmask = a->tapmask ? a->tapmask + (int64_t)g * tiles : nullptr;
+    int rc;
+    const int key = tm * 16 + tn;
+#define WG_CASE(M, N)                                                              \
+  case (M) * 16 + (N):                                                             \
+    rc = vec ? launch_wgrad<M, N, true>(p, zt, st) : launch_wgrad<M, N, false>(p, zt, st); \
+    break;
+    switch (key) {
+      WG_CASE(8, 8) WG_CASE(8, 4) WG_CASE(4, 8) WG_CASE(4, 4)
+      WG_CASE(8, 1) WG_CASE(1, 8) WG_CASE(4, 1) WG_CASE(1, 4) WG_CASE(1, 1)
+      default: PCC_REQUIRE(false, "unreachable tile");
+    }
+#undef WG_CASE
+    if (rc != PCC_OK) return rc;
+  }
+  wgrad_reduce_kernel<<<(unsigned)ceil_div(wn, 256), 256, 0, st>>>(p.part, p.S, wn, a->dweight);
+  PCC_CHECK_LAUNCH("wgrad_reduce_kernel");
+  return PCC_OK;
+}
+
+int pcc_scatter_rows_add(const float* g, int32_t c, const int32_t* rows, int64_t n, float* out, void* stream) {
+  if (n == 0) return PCC_OK;
+  PCC_REQUIRE(g && out && c > 0, "bad argument");
+  scatter_rows_add_kernel<<<(unsigned)ceil_div(n * c, 256), 256, 0, (cudaStream_t)stream>>>(g, c, rows, n, out);
+  PCC_CHECK_LAUNCH("scatter_rows_add_kernel");
+  return PCC_OK;
+}
+
+int pcc_gc_likelihood_train_fwd(const float* y_noisy, const float* params, const int32_t* rows, int64_t n,
+                                int32_t c, float scale_bound, float likelihood_bound, float* likelihood,
+                                void* stream) {
+  if (n == 0) return PCC_OK;
+  PCC_REQUIRE(y_noisy && params && likelihood && c > 0, "bad argument");
+  gc_train_fwd_kernel<<<(unsigned)ceil_div(n * c, 256), 256, 0, (cudaStream_t)stream>>>(
+      y_noisy, params, rows, n, c, scale_bound, likelihood_bound, likelihood);
+  PCC_CHECK_LAUNCH("gc_train_fwd_kernel");
+  return PCC_OK;
+}
+
+int pcc_gc_likelihood_train_bwd(const float* y_noisy, const float* params, const int32_t* rows, int64_t n,
+                                int32_t c, float scale_bound, float likelihood_bound, const float* g_likelihood,
+                                float* g_y, float* g_param_rows, void* stream) {
+  if (n == 0) return PCC_OK;
+  PCC_REQUIRE(y_noisy && params && g_likelihood && g_y && g_param_rows && c > 0, "bad argument");
+  gc_train_bwd_kernel<<<(unsigned)ceil_div(n * c, 256), 256, 0, (cudaStream_t)stream>>>(
+      y_noisy, params, rows, n, c, scale_bound, likelihood_bound, g_likelihood, g_y, g_param_rows);
+  PCC_CHECK_LAUNCH("gc_train_bwd_kernel");
+  return PCC_OK;
+}
+
+}  // extern "C"

@@ -10,7 +10,7 @@ import weakref
 import torch
 
 from . import _lib
-from ._lib import ConvArgs, check
+from ._lib import ConvArgs, WgradArgs, check
 
 TILE_M = 128
 ACT_NONE, ACT_RELU, ACT_LEAKY = 0, 1, 2
@@ -486,6 +486,73 @@ def gather_rows(feats, rows, add=None):
     if n:
         _count()
     return out
+
+
+def conv_wgrad(feats, gout, kmap, cin, cout):
+    """Weight gradient of conv(): dW[k] = sum_j feats[nbr[k][j]]^T (x) gout[order[j]]  -> [K, cin, cout].
+    Deterministic (fixed summation order).  SURVEY.md §8f row 4; ME ConvolutionBackward's grad_kernel."""
+    _need_cuda(feats, "feats")
+    feats, gout = feats.contiguous(), gout.contiguous()
+    K = kmap.K
+    if feats.shape[1] != cin or gout.shape[1] != cout or gout.shape[0] != kmap.n_out:
+        raise _lib.PccError(f"conv_wgrad shape mismatch: feats {tuple(feats.shape)}, gout {tuple(gout.shape)}, "
+                            f"n_out {kmap.n_out}")
+    dw = torch.empty((K, cin, cout), dtype=torch.float32, device=feats.device)
+    wsb = _L().pcc_conv_wgrad_ws_bytes(K, cin, cout)
+    ws = _ws(wsb, feats.device)
+    a = WgradArgs()
+    a.in_, a.gout, a.cin, a.cout = feats.data_ptr(), gout.data_ptr(), cin, cout
+    a.nbr, a.nbr_stride = kmap.nbr.data_ptr(), kmap.stride
+    a.tapmask = kmap.tapmask.data_ptr()
+    a.order = None if kmap.order is None else kmap.order.data_ptr()
+    a.n_out, a.K, a.n_groups = kmap.n_out, K, kmap.n_groups
+    a.dweight, a.ws, a.ws_bytes = dw.data_ptr(), ws.data_ptr(), wsb
+    if _profile is not None and kmap.n_out:
+        rec = {"cin": cin, "cout": cout, "K": K, "n_in": int(feats.shape[0]), "n_out": int(kmap.n_out),
+               "pairs": _pairs(kmap), "mode": -1, "ev0": torch.cuda.Event(enable_timing=True),
+               "ev1": torch.cuda.Event(enable_timing=True)}
+        rec["ev0"].record()
+        check(_L().pcc_conv_wgrad(ctypes.byref(a), _stream()), "pcc_conv_wgrad")
+        rec["ev1"].record()
+        _profile.append(rec)
+    else:
+        check(_L().pcc_conv_wgrad(ctypes.byref(a), _stream()), "pcc_conv_wgrad")
+    _count(kmap.n_groups + 1)
+    return dw
+
+
+def scatter_rows_add(g, rows, n_dst):
+    """Backward of gather_rows: out [n_dst, c] with out[rows[i]] += g[i] (rows < 0 skipped)."""
+    g = g.contiguous()
+    out = torch.zeros((n_dst, g.shape[1]), dtype=torch.float32, device=g.device)
+    check(_L().pcc_scatter_rows_add(_ptr(g), g.shape[1], _ptr(rows), g.shape[0], _ptr(out), _stream()),
+          "pcc_scatter_rows_add")
+    if g.shape[0]:
+        _count()
+    return out
+
+
+def gc_likelihood_train_fwd(y_noisy, params, rows, scale_bound, lik_bound):
+    """-> likelihood [N, C] (row-major) of noise-quantised latents (GaussianConditional, training)."""
+    n, c = y_noisy.shape
+    lik = torch.empty((n, c), dtype=torch.float32, device=y_noisy.device)
+    check(_L().pcc_gc_likelihood_train_fwd(_ptr(y_noisy.contiguous()), _ptr(params.contiguous()), _ptr(rows), n, c,
+                                           scale_bound, lik_bound, _ptr(lik), _stream()),
+          "pcc_gc_likelihood_train_fwd")
+    _count()
+    return lik
+
+
+def gc_likelihood_train_bwd(y_noisy, params, rows, scale_bound, lik_bound, g_lik):
+    """-> (g_y [N, C], g_param_rows [N, 2C])."""
+    n, c = y_noisy.shape
+    g_y = torch.empty((n, c), dtype=torch.float32, device=y_noisy.device)
+    g_p = torch.empty((n, 2 * c), dtype=torch.float32, device=y_noisy.device)
+    check(_L().pcc_gc_likelihood_train_bwd(_ptr(y_noisy.contiguous()), _ptr(params.contiguous()), _ptr(rows), n, c,
+                                           scale_bound, lik_bound, _ptr(g_lik.contiguous()), _ptr(g_y), _ptr(g_p),
+                                           _stream()), "pcc_gc_likelihood_train_bwd")
+    _count()
+    return g_y, g_p
 
 
 def take_keys(keys, rows):

@@ -50,3 +50,28 @@ def roi_q_map(points, q_g, q_a, axis, plane):
     """Region-of-interest map (evaluate_view_dep.py:252-258): full quality at and beyond `plane`."""
     s = roi_scores(points, axis, plane)
     return q_map(points, q_g * s, q_a * s)
+
+
+Q_MAP_CONFIG = {"lambda_A_min": 0, "lambda_A_max": 6400, "lambda_G_min": 0, "lambda_G_max": 200,
+                "mode": "exponential"}  # configs/Ours.yaml:38-43
+
+
+def lambda_map(q_feats, config=None):
+    """Training-time loss weights of a quality map (data/q_map.py:188-205, ``scale_q_map``):
+    column 0 (geometry) and 1 (attribute) of Q in [0, 1] -> lambda in [lambda_min, lambda_max]."""
+    import math
+    cfg = Q_MAP_CONFIG if config is None else config
+    out = q_feats.clone().to(torch.float32)
+    if cfg["mode"] == "exponential":
+        a_A, b_A = math.log2(cfg["lambda_A_max"] + cfg["lambda_A_min"]), cfg["lambda_A_min"] - 1
+        a_G, b_G = math.log2(cfg["lambda_G_max"] + cfg["lambda_G_min"]), cfg["lambda_G_min"] - 1
+        out[:, 0] = 2 ** (out[:, 0] * a_G) + b_G
+        out[:, 1] = 2 ** (out[:, 1] * a_A) + b_A
+    elif cfg["mode"] == "quadratic":
+        a_A, b_A = cfg["lambda_A_max"] - cfg["lambda_A_min"], cfg["lambda_A_min"]
+        a_G, b_G = cfg["lambda_G_max"] - cfg["lambda_G_min"], cfg["lambda_G_min"]
+        out[:, 0] = out[:, 0] ** 2 * a_G + b_G
+        out[:, 1] = out[:, 1] ** 2 * a_A + b_A
+    else:
+        raise ValueError("Unknown Q_map mode")
+    return out

@@ -1,0 +1,282 @@
+"""GPU parity of the training path, through the C-ABI.
+
+* operator level: data / weight / bias gradients of the sparse convolution, the row gather and the
+  training-mode Gaussian likelihood against torch CPU autograd over the ORACLE's kernel maps
+  (oracle.train_shims) — float tolerance: the gradient sums run in a different fp32 order;
+* adjoint identities that hold at any size: <G, conv(x, W)> = <dgrad(G), x> = <wgrad(x, G), W>;
+* model level: the fixtures of tests/golden/make_golden_train.py (the reference's OWN
+  ColorModel.forward and loss.py, run under CPU autograd) — loss terms and every parameter gradient.
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import random_cloud
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+HERE = os.path.dirname(os.path.abspath(__file__))
+TRAIN_GOLDEN = sorted(glob.glob(os.path.join(HERE, "golden", "train_*.npz")))
+
+# fp32 sums of up to ~1e5 terms in another order than the CPU's: relative to the tensor's largest entry
+RTOL = 2e-4
+
+
+def _close(got, ref, rtol=RTOL, what=""):
+    got, ref = np.asarray(got, np.float64), np.asarray(ref, np.float64)
+    scale = max(np.abs(ref).max(), 1e-30)
+    err = np.abs(got - ref).max() / scale
+    assert err <= rtol, f"{what}: max error {err:.3e} of the largest entry (tolerance {rtol})"
+
+
+def _maps(pcc, oracle, n, extent, ts, seed, ks, stride, transpose):
+    c = random_cloud(n, extent, seed, 1, -2)
+    c[:, 1:] *= ts
+    m, _ = pcc.ops.canonical_map(torch.from_numpy(c).to(DEV), ts)
+    keys = np.sort(oracle.prims.pack_keys(c))
+    cs = oracle.prims.unpack_keys(keys)
+    P = oracle.prims
+    if transpose:
+        out_map = m.expand(ks)
+        out_coords = P.expand_coords(cs, ks, ts // 2)
+        offs = -P.kernel_offsets(ks) * (ts // 2)
+    elif stride == 2:
+        out_map = m.stride2()
+        out_coords = P.stride_coords(cs, ts * 2)
+        offs = P.kernel_offsets(ks) * ts
+    else:
+        out_map, out_coords, offs = m, cs, P.kernel_offsets(ks) * ts
+    nbr = P.kernel_map(keys, out_coords, offs)
+    assert out_map.n == out_coords.shape[0]
+    return m, out_map, nbr
+
+
+@pytest.mark.parametrize("cin,cout,ks,stride,transpose,groups", [
+    (128, 128, 3, 1, False, None), (64, 64, 3, 1, False, 3), (4, 64, 3, 1, False, None), (2, 2, 3, 1, False, None),
+    (128, 4, 3, 1, False, 1), (32, 3, 3, 1, False, None), (16, 16, 1, 1, False, None), (64, 128, 3, 2, False, None),
+    (128, 64, 3, 2, True, None), (128, 192, 2, 2, True, None), (2, 2, 3, 2, True, None), (128, 256, 3, 1, False, None),
+    (20, 35, 3, 1, False, 2)])
+def test_conv_gradients_match_cpu_autograd(pcc, oracle, cin, cout, ks, stride, transpose, groups):
+    from oracle import train_shims as TS
+    rng = np.random.default_rng(cin * 131 + cout * 7 + ks + stride)
+    pcc.ops.set_tap_groups(groups)
+    try:
+        m, out_map, nbr = _maps(pcc, oracle, 3000, 22, 4, cin + cout, ks, stride, transpose)
+        x = rng.standard_normal((m.n, cin)).astype(np.float32)
+        shape = (ks ** 3, cin, cout) if ks > 1 else (cin, cout)
+        W = (rng.standard_normal(shape) / np.sqrt(cin * 4)).astype(np.float32)
+        b = rng.standard_normal((1, cout)).astype(np.float32)
+        G = rng.standard_normal((out_map.n, cout)).astype(np.float32)
+        # oracle: torch CPU autograd over the oracle's kernel map
+        xr, Wr, br = (torch.from_numpy(a.copy()).requires_grad_(True) for a in (x, W, b))
+        ref = TS._conv_apply(xr, nbr, Wr, br, out_map.n)
+        ref.backward(torch.from_numpy(G))
+        # product
+        xg, Wg, bg = (torch.from_numpy(a.copy()).to(DEV).requires_grad_(True) for a in (x, W, b))
+        got = pcc.autograd.sparse_conv(xg, m, out_map, ks, Wg, bg, transpose=transpose)
+        got.backward(torch.from_numpy(G).to(DEV))
+    finally:
+        pcc.ops.set_tap_groups(None)
+    _close(got.detach().cpu().numpy(), ref.detach().numpy(), what="forward")
+    _close(xg.grad.cpu().numpy(), xr.grad.numpy(), what="data gradient")
+    _close(Wg.grad.cpu().numpy(), Wr.grad.numpy(), what="weight gradient")
+    _close(bg.grad.cpu().numpy(), br.grad.numpy(), what="bias gradient")
+
+
+def test_weight_gradient_is_deterministic(pcc, oracle):
+    rng = np.random.default_rng(5)
+    m, out_map, _ = _maps(pcc, oracle, 6000, 26, 1, 3, 3, 1, False)
+    x = torch.from_numpy(rng.standard_normal((m.n, 64)).astype(np.float32)).to(DEV)
+    G = torch.from_numpy(rng.standard_normal((m.n, 128)).astype(np.float32)).to(DEV)
+    km = m.kernel_map(m, 3)
+    a = pcc.ops.conv_wgrad(x, G, km, 64, 128)
+    b = pcc.ops.conv_wgrad(x, G, km, 64, 128)
+    assert torch.equal(a, b)
+
+
+def test_epilogue_gradients(pcc, oracle):
+    """bias -> ReLU -> FiLM (gathered rows) -> residual, as pcc_conv_fwd orders them."""
+    rng = np.random.default_rng(11)
+    m, _, nbr = _maps(pcc, oracle, 2000, 18, 1, 9, 3, 1, False)
+    c = 32
+    t = lambda a: torch.from_numpy(a.astype(np.float32))
+    x, W, b = t(rng.standard_normal((m.n, c))), t(rng.standard_normal((27, c, c)) / 12), t(rng.standard_normal((1, c)))
+    film, res = t(rng.standard_normal((m.n + 5, 2 * c))), t(rng.standard_normal((m.n, c)))
+    rows = rng.permutation(m.n + 5)[:m.n].astype(np.int32)
+    rows[::7] = -1
+    G = t(rng.standard_normal((m.n, c)))
+    from oracle import train_shims as TS
+    cpu = [a.clone().requires_grad_(True) for a in (x, W, b, film, res)]
+    v = torch.relu(TS._conv_apply(cpu[0], nbr, cpu[1], cpu[2], m.n))
+    hit = torch.from_numpy(rows >= 0).unsqueeze(1).float()
+    f = cpu[3][torch.from_numpy(np.maximum(rows, 0).astype(np.int64))] * hit
+    ref = v * f[:, :c] + f[:, c:] + cpu[4]
+    ref.backward(G)
+    gpu = [a.clone().to(DEV).requires_grad_(True) for a in (x, W, b, film, res)]
+    got = pcc.autograd.sparse_conv(gpu[0], m, m, 3, gpu[1], gpu[2], act=pcc.ops.ACT_RELU, film=gpu[3],
+                                   film_rows=torch.from_numpy(rows).to(DEV), residual=gpu[4])
+    got.backward(G.to(DEV))
+    # the fused inference epilogue computes the same forward value
+    fused = pcc.ops.conv(gpu[0].detach(), m.kernel_map(m, 3), gpu[1].detach(), gpu[2].detach(), act=pcc.ops.ACT_RELU,
+                         film=gpu[3].detach(), film_rows=torch.from_numpy(rows).to(DEV), residual=gpu[4].detach(),
+                         mode=pcc.ops.MODE_EXACT)
+    _close(fused.cpu().numpy(), got.detach().cpu().numpy(), 1e-6, "fused epilogue vs unfused")
+    _close(got.detach().cpu().numpy(), ref.detach().numpy(), what="forward")
+    for name, g, r in zip(("x", "W", "b", "film", "residual"), gpu, cpu):
+        _close(g.grad.cpu().numpy(), r.grad.numpy(), what=f"grad {name}")
+
+
+def test_gaussian_likelihood_training_mode(pcc):
+    from oracle import train_shims as TS
+    rng = np.random.default_rng(3)
+    n, c, p = 700, 24, 500
+    y = torch.from_numpy(rng.standard_normal((n, c)).astype(np.float32) * 3)
+    params = torch.from_numpy(np.concatenate([np.abs(rng.standard_normal((p, c))) * 0.6 + 0.02,
+                                              rng.standard_normal((p, c))], 1).astype(np.float32))
+    params[:, :c][::5] = 0.05        # below the scale bound: LowerBound's gradient rule decides
+    rows = rng.integers(-1, p, size=n).astype(np.int32)
+    G = torch.from_numpy(rng.standard_normal((n, c)).astype(np.float32))
+    gc = TS.GaussianConditional(None)
+    yr, pr = y.clone().requires_grad_(True), params.clone().requires_grad_(True)
+    hit = torch.from_numpy(rows >= 0).unsqueeze(1).float()
+    g = pr[torch.from_numpy(np.maximum(rows, 0).astype(np.int64))] * hit
+    TS.reseed(0)
+    gc.train()
+    out_r, lik_r = gc(yr.t().unsqueeze(0), g[:, :c].t().unsqueeze(0), means=g[:, c:].t().unsqueeze(0))
+    lik_r.backward(G.t().unsqueeze(0))
+    noise = TS.noise_log[0][0].t().contiguous()
+    yg, pg = y.clone().to(DEV).requires_grad_(True), params.clone().to(DEV).requires_grad_(True)
+    y_noisy = yg + noise.to(DEV)
+    lik = pcc.autograd.gc_likelihood(y_noisy, pg, torch.from_numpy(rows).to(DEV), 0.11, 1e-9)
+    lik.backward(G.to(DEV))
+    _close(lik.detach().cpu().numpy(), lik_r[0].t().detach().numpy(), 2e-5, "likelihood")
+    _close(yg.grad.cpu().numpy(), yr.grad.numpy(), 2e-4, "d/dy")
+    _close(pg.grad.cpu().numpy(), pr.grad.numpy(), 2e-4, "d/d(scale, mean)")
+
+
+def test_adjoint_identities_full_size(pcc):
+    """<G, conv(x, W)> == <dgrad(G), x> == <wgrad(x, G), W> on a 250 k-voxel level (the L1 size of the
+    800 k-point frame): holds at any size, checked with the forward kernel as the reference."""
+    x6 = pcc.synthetic.shell_frame(140.0, center=[256] * 3, grid=512, seed=0)
+    pts = torch.cat([torch.zeros((x6.shape[0], 1)), x6[:, :3]], 1).int().to(DEV)
+    m, _ = pcc.ops.canonical_map(pts, 1)
+    assert m.n > 200000
+    g = torch.Generator(device=DEV).manual_seed(0)
+    cin, cout = 64, 128
+    x = torch.randn((m.n, cin), device=DEV, generator=g, requires_grad=True)
+    W = (torch.randn((27, cin, cout), device=DEV, generator=g) / 24).requires_grad_(True)
+    out = pcc.autograd.sparse_conv(x, m, m, 3, W, None)
+    G = torch.randn(out.shape, device=DEV, generator=g)
+    out.backward(G)
+    lhs = (G.double() * out.detach().double()).sum().item()
+    via_x = (x.grad.double() * x.detach().double()).sum().item()
+    via_w = (W.grad.double() * W.detach().double()).sum().item()
+    scale = (G.double().abs() * out.detach().double().abs()).sum().item()
+    assert abs(lhs - via_x) <= 1e-5 * scale and abs(lhs - via_w) <= 1e-5 * scale, (lhs, via_x, via_w, scale)
+
+
+def _golden_batch(pcc, g):
+    class T:  # SparseTensor-like: .C, .F
+        def __init__(self, C, F):
+            self.C, self.F = C, F
+    coords = torch.from_numpy(g["coords"]).to(DEV)
+    return (T(coords, torch.from_numpy(g["colours"]).to(DEV)), T(coords, torch.from_numpy(g["q"]).to(DEV)),
+            T(coords, torch.from_numpy(g["lam"]).to(DEV)))
+
+
+LOSS_CONFIG = {  # configs/Ours.yaml:60-76
+    "Multiscale_FocalLoss": {"type": "Multiscale_FocalLoss", "alpha": 0.5, "gamma": 2.0},
+    "ColorLoss": {"type": "ColorLoss", "loss": "L2"},
+    "bpp-y": {"type": "BPPLoss", "key": "y", "weight": 1.0},
+    "bpp-z": {"type": "BPPLoss", "key": "z", "weight": 1.0},
+}
+
+
+def test_train_fixtures_present():
+    assert len(TRAIN_GOLDEN) >= 2
+
+
+@pytest.mark.parametrize("path", TRAIN_GOLDEN, ids=[os.path.basename(p) for p in TRAIN_GOLDEN])
+def test_training_step_matches_reference_code(pcc, path):
+    """Loss terms and gradients of the reference's ColorModel.forward + loss.py (fixture) reproduced by
+    the CUDA path on the same batch, weights and noise.  Tolerances: loss terms 1e-4 relative;
+    gradients 2e-3 of each tensor's norm (fp32, ~60 layers deep, sums in another order)."""
+    g = np.load(path)
+    cfg = getattr(pcc, str(g["config"]))
+    model = pcc.ColorModel(cfg)
+    pcc.init_synthetic(model, int(g["wseed"]))
+    model.to(DEV).train()
+    x, Q, Lambda = _golden_batch(pcc, g)
+    noise = [torch.from_numpy(g[f"noise{i}"]) for i in range(int(g["n_noise"]))]
+    it = iter(noise)
+
+    def replay(like):
+        n = next(it)
+        if tuple(n.shape) != tuple(like.shape):  # reference layout [1, C, N] / [C, 1, N] -> rows [N, C]
+            n = n.reshape(-1, n.shape[-1]) if n.shape[0] != 1 else n[0]
+            n = n.t() if tuple(n.t().shape) == tuple(like.shape) else n.reshape(like.shape)
+        return n.contiguous()
+
+    pcc.compressai_compat.set_noise_source(replay)
+    try:
+        out = model(x, Q, Lambda)
+        total, parts = pcc.loss.Loss(LOSS_CONFIG)(x, out)
+        total.backward()
+        aux = model.aux_loss()
+        aux.backward()
+    finally:
+        pcc.compressai_compat.set_noise_source(None)
+    for k, v in parts.items():
+        ref = float(g["loss/" + k])
+        assert abs(float(v) - ref) <= 1e-4 * max(abs(ref), 1e-3), (k, float(v), ref)
+    assert abs(float(total) - float(g["total"])) <= 1e-4 * abs(float(g["total"]))
+    assert abs(float(aux) - float(g["aux"])) <= 1e-4 * abs(float(g["aux"]))
+    params = dict(model.named_parameters())
+    worst = 0.0
+    for name in g["grad_names"].tolist():
+        p = params[name] if name in params else dict(model.named_parameters(remove_duplicate=False))[name]
+        assert p.grad is not None, f"no gradient for {name}"
+        flat = p.grad.detach().double().reshape(-1).cpu().numpy()
+        norm = float(g["gnorm/" + name])
+        got_norm = float(np.linalg.norm(flat))
+        assert abs(got_norm - norm) <= 2e-3 * max(norm, 1e-12), (name, got_norm, norm)
+        err = np.abs(flat[g["gidx/" + name]] - g["gval/" + name]).max()
+        assert err <= 2e-3 * max(norm, 1e-12), (name, err, norm)
+        worst = max(worst, err / max(norm, 1e-12))
+    print(f"{os.path.basename(path)}: {len(g['grad_names'])} gradients, worst sampled error {worst:.2e} of the norm")
+
+
+def test_optimizer_step_reduces_loss(pcc):
+    """Three Adam steps on one batch with frozen noise lower the loss (train.py:189-203 loop shape)."""
+    g = np.load(TRAIN_GOLDEN[0])
+    model = pcc.ColorModel(getattr(pcc, str(g["config"])))
+    pcc.init_synthetic(model, 0)
+    model.to(DEV).train()
+    x, Q, Lambda = _golden_batch(pcc, g)
+    loss_fn = pcc.loss.Loss(LOSS_CONFIG)
+    main = [p for n, p in model.named_parameters() if not n.endswith(".quantiles")]
+    opt = torch.optim.Adam(main, lr=1e-4)
+    gens = {}
+
+    def frozen(like):
+        key = tuple(like.shape)
+        if key not in gens:
+            gens[key] = torch.empty(like.shape).uniform_(-0.5, 0.5, generator=torch.Generator().manual_seed(1))
+        return gens[key]
+
+    pcc.compressai_compat.set_noise_source(frozen)
+    try:
+        values = []
+        for _ in range(4):
+            opt.zero_grad()
+            total, _ = loss_fn(x, model(x, Q, Lambda))
+            values.append(float(total))
+            total.backward()
+            torch.nn.utils.clip_grad_norm_(main, 1.0)
+            opt.step()
+    finally:
+        pcc.compressai_compat.set_noise_source(None)
+    assert values[-1] < values[0], values
