@@ -362,17 +362,20 @@ class EntropyBottleneck(EntropyModel):
         z_hat = ops.eb_dequantize(_to_dev(sym, device), med)
         return z_hat.t().unsqueeze(0)
 
-    def _logits_cumulative(self, inputs):
+    def _logits_cumulative(self, inputs, stop_gradient=False):
+        p = (lambda t: t.detach()) if stop_gradient else (lambda t: t)
         logits = inputs
         for i in range(5):
-            logits = torch.matmul(torch.nn.functional.softplus(getattr(self, f"_matrix{i}")), logits)
-            logits = logits + getattr(self, f"_bias{i}")
+            logits = torch.matmul(torch.nn.functional.softplus(p(getattr(self, f"_matrix{i}"))), logits)
+            logits = logits + p(getattr(self, f"_bias{i}"))
             if i < 4:
-                logits = logits + torch.tanh(getattr(self, f"_factor{i}")) * torch.tanh(logits)
+                logits = logits + torch.tanh(p(getattr(self, f"_factor{i}"))) * torch.tanh(logits)
         return logits
 
     def loss(self):
-        logits = self._logits_cumulative(self.quantiles.detach() if False else self.quantiles)
+        """Auxiliary loss (model/model.py:38-47, train.py:199-203): only the quantiles learn from it
+        (CompressAI evaluates the density with stop_gradient=True here)."""
+        logits = self._logits_cumulative(self.quantiles, stop_gradient=True)
         return torch.abs(logits - self.target).sum()
 
 

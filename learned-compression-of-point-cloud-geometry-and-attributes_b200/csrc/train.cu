@@ -29,33 +29,39 @@ __device__ __forceinline__ void cpa_wait() {
   asm volatile("cp.async.wait_group %0;\n" ::"n"(N));
 }
 
-constexpr int WG_THREADS = 256;
 constexpr int WG_ROWS = 32;  // rows per stage
 
 struct WgradParams {
   const float* in;
   const float* gout;
-  const int32_t* nbr;       // this offset group's view: nbr + k * nbr_stride, tile-row indexed
-  const uint32_t* tapmask;  // group's masks or NULL
-  const int32_t* order;     // group's tile row -> output row or NULL
-  float* part;              // [S][K][cin][cout]
+  const int32_t* nbr;       // [K x nbr_stride], tile-row indexed
+  const uint32_t* tapmask;  // this offset group's masks or NULL
+  const int32_t* order;     // this offset group's tile row -> output row or NULL
+  float* part;              // [S * NZ][K][cin][cout]
   int64_t nbr_stride, n_out;
   int cin, cout, K, k_lo, k_hi, S;
 };
 
-// CTA: one offset k, one (ci tile, co tile), row tiles s, s + S, ...  Thread (ty, tx) of a 16 x 16
-// arrangement owns TM x TN elements of the 16 TM x 16 TN tile.
-template <int TM, int TN, bool VEC>
-__global__ void __launch_bounds__(WG_THREADS)
+// CTA: one offset k, one (ci tile, co tile), row tiles s, s + S, ...  The NY x NX x NZ threads form NZ
+// row-split groups of an NY x NX arrangement; thread (tz, ty, tx) owns TM x TN elements of the
+// (NY TM) x (NX TN) channel tile and accumulates the rows r = tz (mod NZ) of every stage.  Wide layers
+// use NZ = 1 (16 x 16 threads, 8 x 8 registers: 128 x 128 channels); narrow ones (the 4-channel heads,
+// the 2-channel quality branch, the xyz/rgb input layer) keep all lanes busy by splitting rows
+// instead of channels.  Every row split writes its own partial tile.
+template <int TM, int TN, int NY, int NX, int NZ, bool VEC>
+__global__ void __launch_bounds__(NY * NX * NZ)
 conv_wgrad_kernel(const WgradParams p) {
-  constexpr int CI_T = 16 * TM, CO_T = 16 * TN;
+  constexpr int THREADS = NY * NX * NZ;
+  constexpr int CI_T = NY * TM, CO_T = NX * TN;
   constexpr int STAGE = WG_ROWS * (CI_T + CO_T);
+  static_assert(WG_ROWS % NZ == 0, "row splits must divide the stage");
   extern __shared__ __align__(16) float smem[];
   __shared__ int32_t s_in[PCC_TILE_M], s_go[PCC_TILE_M];
   const int k = p.k_lo + blockIdx.y;
   const int co_tiles = (p.cout + CO_T - 1) / CO_T;
   const int ci0 = (blockIdx.z / co_tiles) * CI_T, co0 = (blockIdx.z % co_tiles) * CO_T;
-  const int tid = threadIdx.x, ty = tid / 16, tx = tid % 16;
+  const int tid = threadIdx.x;
+  const int tx = tid % NX, ty = (tid / NX) % NY, tz = tid / (NX * NY);
   float acc[TM][TN];
 #pragma unroll
   for (int i = 0; i < TM; ++i)
@@ -66,40 +72,40 @@ conv_wgrad_kernel(const WgradParams p) {
   for (int64_t tile = blockIdx.x; tile < tiles; tile += p.S) {
     if (p.tapmask && !((p.tapmask[tile] >> k) & 1u)) continue;
     __syncthreads();  // previous tile's readers of s_in / s_go and of the stages are done
-    if (tid < PCC_TILE_M) {
-      const int64_t t = tile * PCC_TILE_M + tid;
+    for (int e = tid; e < PCC_TILE_M; e += THREADS) {
+      const int64_t t = tile * PCC_TILE_M + e;
       int32_t ri = -1, ro = -1;
       if (t < p.n_out) {
         ri = __ldg(p.nbr + (int64_t)k * p.nbr_stride + t);
         ro = p.order ? __ldg(p.order + t) : (int32_t)t;
       }
-      s_in[tid] = ri;
-      s_go[tid] = ri >= 0 ? ro : -1;
+      s_in[e] = ri;
+      s_go[e] = ri >= 0 ? ro : -1;
     }
     __syncthreads();
     auto load_stage = [&](int chunk, int buf) {
       float* a_s = smem + buf * STAGE;
       float* g_s = a_s + WG_ROWS * CI_T;
       if (VEC) {
-        for (int e = tid; e < WG_ROWS * (CI_T / 4); e += WG_THREADS) {
+        for (int e = tid; e < WG_ROWS * (CI_T / 4); e += THREADS) {
           const int r = e / (CI_T / 4), c4 = e % (CI_T / 4);
           const int32_t row = s_in[chunk * WG_ROWS + r];
           const bool ok = row >= 0 && ci0 + c4 * 4 < p.cin;
           cpa16(a_s + r * CI_T + c4 * 4, ok ? p.in + (int64_t)row * p.cin + ci0 + c4 * 4 : p.in, ok);
         }
-        for (int e = tid; e < WG_ROWS * (CO_T / 4); e += WG_THREADS) {
+        for (int e = tid; e < WG_ROWS * (CO_T / 4); e += THREADS) {
           const int r = e / (CO_T / 4), c4 = e % (CO_T / 4);
           const int32_t row = s_go[chunk * WG_ROWS + r];
           const bool ok = row >= 0 && co0 + c4 * 4 < p.cout;
           cpa16(g_s + r * CO_T + c4 * 4, ok ? p.gout + (int64_t)row * p.cout + co0 + c4 * 4 : p.gout, ok);
         }
       } else {
-        for (int e = tid; e < WG_ROWS * CI_T; e += WG_THREADS) {
+        for (int e = tid; e < WG_ROWS * CI_T; e += THREADS) {
           const int r = e / CI_T, c = e % CI_T;
           const int32_t row = s_in[chunk * WG_ROWS + r];
           a_s[e] = (row >= 0 && ci0 + c < p.cin) ? __ldg(p.in + (int64_t)row * p.cin + ci0 + c) : 0.f;
         }
-        for (int e = tid; e < WG_ROWS * CO_T; e += WG_THREADS) {
+        for (int e = tid; e < WG_ROWS * CO_T; e += THREADS) {
           const int r = e / CO_T, c = e % CO_T;
           const int32_t row = s_go[chunk * WG_ROWS + r];
           g_s[e] = (row >= 0 && co0 + c < p.cout) ? __ldg(p.gout + (int64_t)row * p.cout + co0 + c) : 0.f;
@@ -121,24 +127,14 @@ conv_wgrad_kernel(const WgradParams p) {
       const float* a_s = smem + (c & 1) * STAGE;
       const float* g_s = a_s + WG_ROWS * CI_T;
 #pragma unroll 4
-      for (int r = 0; r < WG_ROWS; ++r) {
+      for (int r = tz; r < WG_ROWS; r += NZ) {
         float a[TM], b[TN];
-        if (TM % 4 == 0) {
 #pragma unroll
-          for (int i = 0; i < TM; i += 4)
-            *reinterpret_cast<float4*>(a + i) = *reinterpret_cast<const float4*>(a_s + r * CI_T + ty * TM + i);
-        } else {
+        for (int i = 0; i < TM; i += 4)
+          *reinterpret_cast<float4*>(a + i) = *reinterpret_cast<const float4*>(a_s + r * CI_T + ty * TM + i);
 #pragma unroll
-          for (int i = 0; i < TM; ++i) a[i] = a_s[r * CI_T + ty * TM + i];
-        }
-        if (TN % 4 == 0) {
-#pragma unroll
-          for (int j = 0; j < TN; j += 4)
-            *reinterpret_cast<float4*>(b + j) = *reinterpret_cast<const float4*>(g_s + r * CO_T + tx * TN + j);
-        } else {
-#pragma unroll
-          for (int j = 0; j < TN; ++j) b[j] = g_s[r * CO_T + tx * TN + j];
-        }
+        for (int j = 0; j < TN; j += 4)
+          *reinterpret_cast<float4*>(b + j) = *reinterpret_cast<const float4*>(g_s + r * CO_T + tx * TN + j);
 #pragma unroll
         for (int i = 0; i < TM; ++i)
 #pragma unroll
@@ -147,7 +143,7 @@ conv_wgrad_kernel(const WgradParams p) {
       __syncthreads();  // stage (c & 1) is overwritten by the load issued in the next iteration
     }
   }
-  float* dst = p.part + ((int64_t)blockIdx.x * p.K + k) * p.cin * p.cout;
+  float* dst = p.part + (((int64_t)blockIdx.x * NZ + tz) * p.K + k) * p.cin * p.cout;
 #pragma unroll
   for (int i = 0; i < TM; ++i) {
     const int ci = ci0 + ty * TM + i;
@@ -168,6 +164,18 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ part, int S, int64
   dw[i] = s;
 }
 
+// channel-tile shape of one side: c <= 4: 4 x 1 lanes, <= 16: 4 x 4, <= 32: 4 x 8, <= 64: 8 x 8, else 8 x 16
+struct Side { int t, n; };
+static Side side_for(int c) {
+  if (c <= 4) return {4, 1};
+  if (c <= 16) return {4, 4};
+  if (c <= 32) return {4, 8};
+  if (c <= 64) return {8, 8};
+  return {8, 16};
+}
+static int side_idx(int c) { return c <= 4 ? 0 : c <= 16 ? 1 : c <= 32 ? 2 : c <= 64 ? 3 : 4; }
+static int splits_nz(Side a, Side b) { return std::min(32, 256 / (a.n * b.n)); }
+
 static int wgrad_splits(int K, int zt) {
   // about four CTAs per SM over (splits x offsets x channel tiles)
   const int target = 4 * sm_count();
@@ -175,21 +183,43 @@ static int wgrad_splits(int K, int zt) {
   return std::max(1, std::min(s, 64));
 }
 
-template <int TM, int TN, bool VEC>
+template <int TM, int NY, int TN, int NX, bool VEC>
 static int launch_wgrad(const WgradParams& p, int zt, cudaStream_t st) {
-  constexpr size_t smem = 2 * WG_ROWS * (16 * TM + 16 * TN) * sizeof(float);
+  constexpr int NZ = (256 / (NY * NX)) < 32 ? (256 / (NY * NX)) : 32;
+  constexpr size_t smem = 2 * WG_ROWS * (NY * TM + NX * TN) * sizeof(float);
   static bool attr_done = false;
   if (!attr_done) {
-    PCC_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<TM, TN, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PCC_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<TM, TN, NY, NX, NZ, VEC>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_done = true;
   }
   dim3 grid((unsigned)p.S, (unsigned)(p.k_hi - p.k_lo), (unsigned)zt);
-  conv_wgrad_kernel<TM, TN, VEC><<<grid, WG_THREADS, smem, st>>>(p);
+  conv_wgrad_kernel<TM, TN, NY, NX, NZ, VEC><<<grid, NY * NX * NZ, smem, st>>>(p);
   PCC_CHECK_LAUNCH("conv_wgrad_kernel");
   return PCC_OK;
 }
 
-static int tile_for(int c) { return c > 64 ? 8 : c > 16 ? 4 : 1; }
+template <int TM, int NY, bool VEC>
+static int launch_wgrad_co(const WgradParams& p, int zt, int co_idx, cudaStream_t st) {
+  switch (co_idx) {
+    case 0: return launch_wgrad<TM, NY, 4, 1, VEC>(p, zt, st);
+    case 1: return launch_wgrad<TM, NY, 4, 4, VEC>(p, zt, st);
+    case 2: return launch_wgrad<TM, NY, 4, 8, VEC>(p, zt, st);
+    case 3: return launch_wgrad<TM, NY, 8, 8, VEC>(p, zt, st);
+    default: return launch_wgrad<TM, NY, 8, 16, VEC>(p, zt, st);
+  }
+}
+
+template <bool VEC>
+static int launch_wgrad_ci(const WgradParams& p, int zt, int ci_idx, int co_idx, cudaStream_t st) {
+  switch (ci_idx) {
+    case 0: return launch_wgrad_co<4, 1, VEC>(p, zt, co_idx, st);
+    case 1: return launch_wgrad_co<4, 4, VEC>(p, zt, co_idx, st);
+    case 2: return launch_wgrad_co<4, 8, VEC>(p, zt, co_idx, st);
+    case 3: return launch_wgrad_co<8, 8, VEC>(p, zt, co_idx, st);
+    default: return launch_wgrad_co<8, 16, VEC>(p, zt, co_idx, st);
+  }
+}
 
 // ---------------------------------------------------------------- scatter-add of rows
 __global__ void scatter_rows_add_kernel(const float* __restrict__ g, int c, const int32_t* __restrict__ rows,
@@ -267,9 +297,9 @@ using namespace pcc;
 extern "C" {
 
 size_t pcc_conv_wgrad_ws_bytes(int32_t K, int32_t cin, int32_t cout) {
-  const int tm = tile_for(cin), tn = tile_for(cout);
-  const int zt = (int)(ceil_div(cin, 16 * tm) * ceil_div(cout, 16 * tn));
-  return (size_t)wgrad_splits(K, zt) * K * cin * cout * sizeof(float) + 256;
+  const Side a = side_for(cin), b = side_for(cout);
+  const int zt = (int)(ceil_div(cin, a.t * a.n) * ceil_div(cout, b.t * b.n));
+  return (size_t)wgrad_splits(K, zt) * splits_nz(a, b) * K * cin * cout * sizeof(float) + 256;
 }
 
 int pcc_conv_wgrad(const pcc_wgrad_args* a, void* stream) {
@@ -285,13 +315,13 @@ int pcc_conv_wgrad(const pcc_wgrad_args* a, void* stream) {
   PCC_REQUIRE(a->nbr_stride >= a->n_out, "nbr_stride < n_out");
   PCC_REQUIRE(a->ws_bytes >= pcc_conv_wgrad_ws_bytes(a->K, a->cin, a->cout), "workspace too small");
   PCC_REQUIRE(a->n_groups <= 1 || (a->order && a->n_groups <= a->K), "n_groups > 1 needs order and n_groups <= K");
-  const int tm = tile_for(a->cin), tn = tile_for(a->cout);
-  const int zt = (int)(ceil_div(a->cin, 16 * tm) * ceil_div(a->cout, 16 * tn));
+  const Side sa = side_for(a->cin), sb = side_for(a->cout);
+  const int zt = (int)(ceil_div(a->cin, sa.t * sa.n) * ceil_div(a->cout, sb.t * sb.n));
   WgradParams p;
   p.in = a->in; p.gout = a->gout; p.nbr = a->nbr; p.part = reinterpret_cast<float*>(a->ws);
   p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.cin = a->cin; p.cout = a->cout; p.K = a->K;
   p.S = wgrad_splits(a->K, zt);
-  const bool vec = a->cin % 4 == 0 && a->cout % 4 == 0 && tm >= 4 && tn >= 4 &&
+  const bool vec = a->cin % 4 == 0 && a->cout % 4 == 0 &&
                    (reinterpret_cast<uintptr_t>(a->in) & 15) == 0 && (reinterpret_cast<uintptr_t>(a->gout) & 15) == 0;
   const int ng = a->n_groups > 1 ? a->n_groups : 1;
   const int per = (a->K + ng - 1) / ng;
@@ -302,21 +332,11 @@ int pcc_conv_wgrad(const pcc_wgrad_args* a, void* stream) {
     if (p.k_lo >= p.k_hi) break;
     p.order = a->order ? a->order + (int64_t)g * a->n_out : nullptr;
     p.tapmask = a->tapmask ? a->tapmask + (int64_t)g * tiles : nullptr;
-    int rc;
-    const int key = tm * 16 + tn;
-#define WG_CASE(M, N)                                                              \
-  case (M) * 16 + (N):                                                             \
-    rc = vec ? launch_wgrad<M, N, true>(p, zt, st) : launch_wgrad<M, N, false>(p, zt, st); \
-    break;
-    switch (key) {
-      WG_CASE(8, 8) WG_CASE(8, 4) WG_CASE(4, 8) WG_CASE(4, 4)
-      WG_CASE(8, 1) WG_CASE(1, 8) WG_CASE(4, 1) WG_CASE(1, 4) WG_CASE(1, 1)
-      default: PCC_REQUIRE(false, "unreachable tile");
-    }
-#undef WG_CASE
+    const int rc = vec ? launch_wgrad_ci<true>(p, zt, side_idx(a->cin), side_idx(a->cout), st)
+                       : launch_wgrad_ci<false>(p, zt, side_idx(a->cin), side_idx(a->cout), st);
     if (rc != PCC_OK) return rc;
   }
-  wgrad_reduce_kernel<<<(unsigned)ceil_div(wn, 256), 256, 0, st>>>(p.part, p.S, wn, a->dweight);
+  wgrad_reduce_kernel<<<(unsigned)ceil_div(wn, 256), 256, 0, st>>>(p.part, p.S * splits_nz(sa, sb), wn, a->dweight);
   PCC_CHECK_LAUNCH("wgrad_reduce_kernel");
   return PCC_OK;
 }

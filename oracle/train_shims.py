@@ -54,7 +54,7 @@ class SparseTensor:
         if c.is_floating_point():
             c = torch.floor(c)
         self._C = c.to(torch.int32).contiguous()
-        self._F = features.to(torch.float32)
+        self._F = features.to(torch.get_default_dtype())  # fixture scripts may run the tape in float64
         assert self._C.shape[0] == self._F.shape[0]
         ts = tensor_stride[0] if isinstance(tensor_stride, (list, tuple)) else tensor_stride
         self._ts = int(ts)
@@ -85,13 +85,14 @@ class SparseTensor:
 def _conv_apply(F_can, nbr, W, bias, n_out):
     if W.dim() == 2:
         W = W.unsqueeze(0)
+    W = W.to(F_can.dtype)
     out = torch.zeros((n_out, W.shape[2]), dtype=F_can.dtype)
     for k in range(nbr.shape[0]):
         o = np.nonzero(nbr[k] >= 0)[0]
         if o.size:
             out = out.index_add(0, torch.from_numpy(o.astype(np.int64)),
                                 F_can[torch.from_numpy(nbr[k][o].astype(np.int64))] @ W[k])
-    return out if bias is None else out + bias
+    return out if bias is None else out + bias.to(out.dtype)
 
 
 class _ConvBase(RS._ConvBase):
@@ -181,8 +182,9 @@ class MinkowskiAvgPooling(nn.Module):
             out_coords = prims.stride_coords(x._C.numpy()[perm], ts_out)
         nbr = prims.kernel_map(np.ascontiguousarray(keys), out_coords, prims.kernel_offsets(self.kernel_size) * ts)
         c = F_can.shape[1]
-        eye = torch.eye(c + 1).unsqueeze(0).repeat(nbr.shape[0], 1, 1)
-        s = _conv_apply(torch.cat([F_can, torch.ones(F_can.shape[0], 1)], dim=1), nbr, eye, None, out_coords.shape[0])
+        eye = torch.eye(c + 1, dtype=F_can.dtype).unsqueeze(0).repeat(nbr.shape[0], 1, 1)
+        s = _conv_apply(torch.cat([F_can, torch.ones(F_can.shape[0], 1, dtype=F_can.dtype)], dim=1), nbr, eye, None,
+                        out_coords.shape[0])
         n = s[:, c:]
         out = torch.where(n > 0, s[:, :c] / n.clamp(min=1.0), torch.zeros_like(s[:, :c]))
         return SparseTensor(features=out, coordinates=torch.from_numpy(np.ascontiguousarray(out_coords)),
@@ -217,13 +219,14 @@ class EntropyBottleneck(RS.EntropyBottleneck):
         self.channels = channels
         self.likelihood_lower_bound = _LowerBound(1e-9)
 
-    def _logits_cumulative(self, v):
+    def _logits_cumulative(self, v, stop_gradient=False):
+        p = (lambda t: t.detach()) if stop_gradient else (lambda t: t)
         logits = v
         for i in range(5):
-            logits = torch.matmul(torch.nn.functional.softplus(getattr(self, f"_matrix{i}")), logits)
-            logits = logits + getattr(self, f"_bias{i}")
+            logits = torch.matmul(torch.nn.functional.softplus(p(getattr(self, f"_matrix{i}"))), logits)
+            logits = logits + p(getattr(self, f"_bias{i}"))
             if i < 4:
-                logits = logits + torch.tanh(getattr(self, f"_factor{i}")) * torch.tanh(logits)
+                logits = logits + torch.tanh(p(getattr(self, f"_factor{i}"))) * torch.tanh(logits)
         return logits
 
     def forward(self, x, training=None):
@@ -241,7 +244,8 @@ class EntropyBottleneck(RS.EntropyBottleneck):
         return outputs.reshape(shape).permute(1, 0, 2), lik.reshape(shape).permute(1, 0, 2)
 
     def loss(self):
-        return torch.abs(self._logits_cumulative(self.quantiles) - self.target).sum()
+        # compressai 1.2.4: _logits_cumulative(self.quantiles, stop_gradient=True) — only the quantiles learn
+        return torch.abs(self._logits_cumulative(self.quantiles, stop_gradient=True) - self.target).sum()
 
 
 class GaussianConditional(RS.GaussianConditional):

@@ -58,7 +58,8 @@ def _maps(pcc, oracle, n, extent, ts, seed, ks, stride, transpose):
     (128, 128, 3, 1, False, None), (64, 64, 3, 1, False, 3), (4, 64, 3, 1, False, None), (2, 2, 3, 1, False, None),
     (128, 4, 3, 1, False, 1), (32, 3, 3, 1, False, None), (16, 16, 1, 1, False, None), (64, 128, 3, 2, False, None),
     (128, 64, 3, 2, True, None), (128, 192, 2, 2, True, None), (2, 2, 3, 2, True, None), (128, 256, 3, 1, False, None),
-    (20, 35, 3, 1, False, 2)])
+    (20, 35, 3, 1, False, 2), (64, 4, 3, 1, False, None), (2, 128, 3, 1, False, None), (16, 2, 3, 1, False, None),
+    (128, 64, 3, 1, False, None), (1, 1, 3, 2, False, None)])
 def test_conv_gradients_match_cpu_autograd(pcc, oracle, cin, cout, ks, stride, transpose, groups):
     from oracle import train_shims as TS
     rng = np.random.default_rng(cin * 131 + cout * 7 + ks + stride)
@@ -202,8 +203,10 @@ def test_train_fixtures_present():
 @pytest.mark.parametrize("path", TRAIN_GOLDEN, ids=[os.path.basename(p) for p in TRAIN_GOLDEN])
 def test_training_step_matches_reference_code(pcc, path):
     """Loss terms and gradients of the reference's ColorModel.forward + loss.py (fixture) reproduced by
-    the CUDA path on the same batch, weights and noise.  Tolerances: loss terms 1e-4 relative;
-    gradients 2e-3 of each tensor's norm (fp32, ~60 layers deep, sums in another order)."""
+    the CUDA path on the same batch, weights and noise.  The fixture's tape ran in float64.  Tolerances:
+    loss terms 1e-4 relative; each gradient (norm and 16 sampled entries) within max(5e-4, 4 x gdev32) of
+    its norm, gdev32 being the deviation of a float32 CPU evaluation of the reference code from the float64
+    gradient (stored in the fixture: the product is held to the accuracy fp32 itself allows there)."""
     g = np.load(path)
     cfg = getattr(pcc, str(g["config"]))
     model = pcc.ColorModel(cfg)
@@ -235,17 +238,19 @@ def test_training_step_matches_reference_code(pcc, path):
     assert abs(float(total) - float(g["total"])) <= 1e-4 * abs(float(g["total"]))
     assert abs(float(aux) - float(g["aux"])) <= 1e-4 * abs(float(g["aux"]))
     params = dict(model.named_parameters())
-    worst = 0.0
+    worst, bad = 0.0, []
     for name in g["grad_names"].tolist():
         p = params[name] if name in params else dict(model.named_parameters(remove_duplicate=False))[name]
         assert p.grad is not None, f"no gradient for {name}"
         flat = p.grad.detach().double().reshape(-1).cpu().numpy()
         norm = float(g["gnorm/" + name])
         got_norm = float(np.linalg.norm(flat))
-        assert abs(got_norm - norm) <= 2e-3 * max(norm, 1e-12), (name, got_norm, norm)
         err = np.abs(flat[g["gidx/" + name]] - g["gval/" + name]).max()
-        assert err <= 2e-3 * max(norm, 1e-12), (name, err, norm)
+        tol = max(5e-4, 4.0 * float(g["gdev32/" + name])) * max(norm, 1e-12)
+        if abs(got_norm - norm) > tol or err > tol:
+            bad.append((name, got_norm, norm, err, tol))
         worst = max(worst, err / max(norm, 1e-12))
+    assert not bad, bad
     print(f"{os.path.basename(path)}: {len(g['grad_names'])} gradients, worst sampled error {worst:.2e} of the norm")
 
 

@@ -124,11 +124,11 @@ def test_fixture_regenerates_from_reference_code(pcc, oracle):
     import yaml
     from oracle import train_shims as TS
     sys.path.insert(0, os.path.join(HERE, "golden"))
-    import make_golden_train as MG
     g = np.load(os.path.join(HERE, "golden", "train_ablation_b1.npz"))
     full = yaml.safe_load(open("/root/reference/configs/Ours.yaml"))
     cfg = yaml.safe_load(open("/root/reference/configs/Ablation_NoCondition_Convolution.yaml"))["model"]
     saved = {k: sys.modules.get(k) for k in TS.NAMES}
+    torch.set_default_dtype(torch.float64)  # the fixture's tape is float64
     try:
         ref_model, ref_loss = TS.load_reference(cfg)
         ours = pcc.ColorModel(cfg)
@@ -142,10 +142,11 @@ def test_fixture_regenerates_from_reference_code(pcc, oracle):
         Lam = ME.SparseTensor(coordinates=coords, features=torch.from_numpy(g["lam"]))
         TS.reseed(1234 + int(g["wseed"]))
         total, parts = ref_loss.Loss({k: dict(v) for k, v in full["loss"].items()})(x, ref_model(x, Q, Lam))
-        assert float(total) == pytest.approx(float(g["total"]), rel=1e-5)
+        assert float(total.detach()) == pytest.approx(float(g["total"]), rel=1e-9)
         for k, v in parts.items():
-            assert float(v) == pytest.approx(float(g["loss/" + k]), rel=1e-5)
+            assert float(v.detach()) == pytest.approx(float(g["loss/" + k]), rel=1e-9)
     finally:
+        torch.set_default_dtype(torch.float32)
         for k, v in saved.items():
             if v is None:
                 sys.modules.pop(k, None)
