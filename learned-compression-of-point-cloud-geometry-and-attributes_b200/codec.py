@@ -82,7 +82,7 @@ class ST:
 def apply_conv(x, layer, out_map=None, transpose=False, **epilogue):
     """One fused convolution: x (ST) -> ST on out_map (default: same map)."""
     out_map = x.m if out_map is None else out_map
-    if AG.wants_grad(x.F, layer.kernel, epilogue.get("film"), epilogue.get("residual")):
+    if layer.training and AG.wants_grad(x.F, layer.kernel, epilogue.get("film"), epilogue.get("residual")):
         # training (model/model.py:51-93 under autograd): same operator, epilogue unfused
         return ST(AG.sparse_conv(x.F, x.m, out_map, layer.kernel_size, layer.kernel, layer.bias,
                                  transpose=transpose, **epilogue), out_map)
@@ -214,7 +214,7 @@ class GenerativeUpBlock(nn.Module):
         if full:
             return apply_conv(t, self.occ_predict[2]).F
         last = self.occ_predict[2]
-        if AG.wants_grad(t.F, last.kernel):  # only channel 0 reaches the loss (loss.py:170): same gradient
+        if last.training and AG.wants_grad(t.F, last.kernel):  # only channel 0 reaches the loss (loss.py:170)
             c = min(4, last.out_channels)
             return AG.sparse_conv(t.F, x.m, x.m, 3, last.kernel[:, :, :c], last.bias[:, :c])
         w, b = self._occ_head()

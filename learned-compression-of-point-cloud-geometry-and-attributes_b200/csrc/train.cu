@@ -31,6 +31,19 @@ __device__ __forceinline__ void cpa_wait() {
 
 constexpr int WG_ROWS = 32;  // rows per stage
 
+// packed fma.rn.f32x2: two independent IEEE fp32 FMAs per issue slot (as conv_exact.cu)
+__device__ __forceinline__ unsigned long long wg_pack2(float lo, float hi) {
+  unsigned long long v;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(v) : "f"(lo), "f"(hi));
+  return v;
+}
+__device__ __forceinline__ void wg_unpack2(unsigned long long v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ void wg_ffma2(unsigned long long& d, unsigned long long a, unsigned long long b) {
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
+}
+
 struct WgradParams {
   const float* in;
   const float* gout;
@@ -62,11 +75,11 @@ conv_wgrad_kernel(const WgradParams p) {
   const int ci0 = (blockIdx.z / co_tiles) * CI_T, co0 = (blockIdx.z % co_tiles) * CO_T;
   const int tid = threadIdx.x;
   const int tx = tid % NX, ty = (tid / NX) % NY, tz = tid / (NX * NY);
-  float acc[TM][TN];
+  unsigned long long acc2[TM][TN / 2];
 #pragma unroll
   for (int i = 0; i < TM; ++i)
 #pragma unroll
-    for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+    for (int j = 0; j < TN / 2; ++j) acc2[i][j] = 0ull;
 
   const int64_t tiles = (p.n_out + PCC_TILE_M - 1) / PCC_TILE_M;
   for (int64_t tile = blockIdx.x; tile < tiles; tile += p.S) {
@@ -135,14 +148,24 @@ conv_wgrad_kernel(const WgradParams p) {
 #pragma unroll
         for (int j = 0; j < TN; j += 4)
           *reinterpret_cast<float4*>(b + j) = *reinterpret_cast<const float4*>(g_s + r * CO_T + tx * TN + j);
+        unsigned long long bp[TN / 2];
 #pragma unroll
-        for (int i = 0; i < TM; ++i)
+        for (int j = 0; j < TN / 2; ++j) bp[j] = wg_pack2(b[2 * j], b[2 * j + 1]);
 #pragma unroll
-          for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        for (int i = 0; i < TM; ++i) {
+          const unsigned long long aa = wg_pack2(a[i], a[i]);
+#pragma unroll
+          for (int j = 0; j < TN / 2; ++j) wg_ffma2(acc2[i][j], aa, bp[j]);
+        }
       }
       __syncthreads();  // stage (c & 1) is overwritten by the load issued in the next iteration
     }
   }
+  float acc[TM][TN];
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < TN / 2; ++j) wg_unpack2(acc2[i][j], acc[i][2 * j], acc[i][2 * j + 1]);
   float* dst = p.part + (((int64_t)blockIdx.x * NZ + tz) * p.K + k) * p.cin * p.cout;
 #pragma unroll
   for (int i = 0; i < TM; ++i) {
@@ -176,11 +199,13 @@ static Side side_for(int c) {
 static int side_idx(int c) { return c <= 4 ? 0 : c <= 16 ? 1 : c <= 32 ? 2 : c <= 64 ? 3 : 4; }
 static int splits_nz(Side a, Side b) { return std::min(32, 256 / (a.n * b.n)); }
 
-static int wgrad_splits(int K, int zt) {
-  // about four CTAs per SM over (splits x offsets x channel tiles)
+constexpr int WG_MAX_SPLITS = 64;
+static int wgrad_splits(int k_launch, int zt, int64_t tiles) {
+  // about four CTAs per SM over (splits x offsets of the launch x channel tiles); never more splits than row tiles
   const int target = 4 * sm_count();
-  int s = target / std::max(1, K * zt);
-  return std::max(1, std::min(s, 64));
+  int64_t s = target / std::max(1, k_launch * zt);
+  s = std::min<int64_t>(s, tiles);
+  return (int)std::max<int64_t>(1, std::min<int64_t>(s, WG_MAX_SPLITS));
 }
 
 template <int TM, int NY, int TN, int NX, bool VEC>
@@ -298,8 +323,8 @@ extern "C" {
 
 size_t pcc_conv_wgrad_ws_bytes(int32_t K, int32_t cin, int32_t cout) {
   const Side a = side_for(cin), b = side_for(cout);
-  const int zt = (int)(ceil_div(cin, a.t * a.n) * ceil_div(cout, b.t * b.n));
-  return (size_t)wgrad_splits(K, zt) * splits_nz(a, b) * K * cin * cout * sizeof(float) + 256;
+  // sized for the largest split count a launch may pick (it depends on the offset groups of the map)
+  return (size_t)WG_MAX_SPLITS * splits_nz(a, b) * K * cin * cout * sizeof(float) + 256;
 }
 
 int pcc_conv_wgrad(const pcc_wgrad_args* a, void* stream) {
@@ -320,12 +345,12 @@ int pcc_conv_wgrad(const pcc_wgrad_args* a, void* stream) {
   WgradParams p;
   p.in = a->in; p.gout = a->gout; p.nbr = a->nbr; p.part = reinterpret_cast<float*>(a->ws);
   p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.cin = a->cin; p.cout = a->cout; p.K = a->K;
-  p.S = wgrad_splits(a->K, zt);
-  const bool vec = a->cin % 4 == 0 && a->cout % 4 == 0 &&
-                   (reinterpret_cast<uintptr_t>(a->in) & 15) == 0 && (reinterpret_cast<uintptr_t>(a->gout) & 15) == 0;
   const int ng = a->n_groups > 1 ? a->n_groups : 1;
   const int per = (a->K + ng - 1) / ng;
   const int64_t tiles = ceil_div(a->n_out, PCC_TILE_M);
+  p.S = wgrad_splits(per, zt, tiles);  // the same for every group: the partial buffer is [S * NZ][K]
+  const bool vec = a->cin % 4 == 0 && a->cout % 4 == 0 &&
+                   (reinterpret_cast<uintptr_t>(a->in) & 15) == 0 && (reinterpret_cast<uintptr_t>(a->gout) & 15) == 0;
   for (int g = 0; g < ng; ++g) {
     p.k_lo = g * per;
     p.k_hi = std::min((g + 1) * per, (int)a->K);

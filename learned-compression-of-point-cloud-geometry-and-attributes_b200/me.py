@@ -111,7 +111,8 @@ class SparseTensor:
             q = torch.floor(q)
         qkeys, _ = ops.pack_coords(q.to(torch.int32))
         rows = self.cmap.lookup(qkeys)
-        return ops.gather_rows(self._F, rows)
+        from . import autograd as AG
+        return AG.gather(self._F, rows) if AG.wants_grad(self._F) else ops.gather_rows(self._F, rows)
 
 
 def _replace(x, feats, cmap=None):
@@ -169,7 +170,14 @@ class _ConvBase(nn.Module):
         if coordinates is not None:
             raise PccError("explicit output coordinates are not on the codec path")
         out_map, kmap = self._maps(input)
-        feats = ops.conv(input.F, kmap, self.kernel, self.bias, act=act)
+        from . import autograd as AG
+        if self.training and AG.wants_grad(input.F, self.kernel):
+            # train() mode under autograd (train.py:189-191): ME's ConvolutionBackward is the data gradient
+            # over the reversed kernel map + pcc_conv_wgrad (autograd.py)
+            feats = AG.sparse_conv(input.F, input.cmap, out_map, self.kernel_size, self.kernel, self.bias,
+                                   transpose=self.is_transpose, act=act)
+        else:
+            feats = ops.conv(input.F, kmap, self.kernel, self.bias, act=act)
         return _replace(input, feats, out_map)
 
     def extra_repr(self):
@@ -216,6 +224,7 @@ class MinkowskiPruning(nn.Module):
     def forward(self, input, mask):
         rows = torch.nonzero(mask.to(input.device).reshape(-1)).reshape(-1).to(torch.int32)
         keys = ops.take_keys(input.cmap.keys, rows)
-        feats = ops.gather_rows(input.F, rows)
+        from . import autograd as AG
+        feats = AG.gather(input.F, rows) if AG.wants_grad(input.F) else ops.gather_rows(input.F, rows)
         cmap = ops.CoordMap(keys, input.cmap.ts, input.cmap.is_sorted)
         return SparseTensor(feats, _cmap=cmap, _manager=CoordinateManager())

@@ -285,3 +285,48 @@ def test_optimizer_step_reduces_loss(pcc):
     finally:
         pcc.compressai_compat.set_noise_source(None)
     assert values[-1] < values[0], values
+
+
+def test_me_shaped_modules_are_differentiable(pcc):
+    """Option A of INTEGRATION.md (the reference's layer-by-layer code over pcc_b200.me): in train() mode the
+    ME-shaped modules record the same gradients as CPU autograd over the oracle stand-ins."""
+    from oracle import train_shims as TS
+    ME = pcc.me
+    rng = np.random.default_rng(4)
+    c = random_cloud(1500, 16, 2, 2, 0)
+    feats = rng.standard_normal((c.shape[0], 6)).astype(np.float32)
+
+    def chain(mod, dev):
+        torch.manual_seed(0)
+        layers = [mod.MinkowskiConvolution(6, 16, kernel_size=3, bias=True, dimension=3),
+                  mod.MinkowskiConvolution(16, 32, kernel_size=3, stride=2, bias=True, dimension=3),
+                  mod.MinkowskiGenerativeConvolutionTranspose(32, 8, kernel_size=3, stride=2, bias=True, dimension=3),
+                  mod.MinkowskiConvolution(8, 8, kernel_size=1, bias=False, dimension=3)]
+        return [l.to(dev) for l in layers], mod.MinkowskiReLU(), mod.MinkowskiPruning()
+
+    gl, grelu, gprune = chain(ME, DEV)
+    cl, crelu, cprune = chain(TS, "cpu")
+    for a, b in zip(gl, cl):
+        with torch.no_grad():
+            b.kernel.copy_(a.kernel.detach().cpu())
+            if a.bias is not None:
+                b.bias.copy_(a.bias.detach().cpu())
+    outs = []
+    for mod, layers, relu, prune, dev in ((ME, gl, grelu, gprune, DEV), (TS, cl, crelu, cprune, "cpu")):
+        f = torch.from_numpy(feats).to(dev).requires_grad_(True)
+        st = mod.SparseTensor(features=f, coordinates=torch.from_numpy(c).to(dev))
+        y = layers[2](relu(layers[1](relu(layers[0](st)))))
+        keep = (y.C[:, 1] % 3 != 0)
+        y = layers[3](prune(y, keep))
+        at = y.features_at_coordinates(st.C.float())
+        loss = (at ** 2).sum() + y.F.sum()
+        loss.backward()
+        outs.append((float(loss.detach()), f.grad.cpu().numpy(), [l.kernel.grad.cpu().numpy() for l in layers],
+                     [l.bias.grad.cpu().numpy() for l in layers if l.bias is not None]))
+    (lg, fg, kg, bg), (lc, fc, kc, bc) = outs
+    assert abs(lg - lc) <= 1e-5 * abs(lc)
+    _close(fg, fc, what="input gradient")
+    for i, (a, b) in enumerate(zip(kg, kc)):
+        _close(a, b, what=f"kernel gradient {i}")
+    for i, (a, b) in enumerate(zip(bg, bc)):
+        _close(a, b, what=f"bias gradient {i}")

@@ -75,7 +75,9 @@ def main():
         aux = model.aux_loss()
         aux.backward()
         aux_opt.step()
-        return float(total)
+        if os.environ.get("PCC_TRAIN_VERBOSE"):
+            print({k: round(float(v.detach()), 4) for k, v in parts.items()}, "aux", round(float(aux.detach()), 2), file=sys.stderr)
+        return float(total.detach())
 
     for _ in range(a.warmup):
         step()
