@@ -42,9 +42,11 @@ def parse_args():
     ap.add_argument("--config", default="ours", choices=["ours", "ablation"])
     ap.add_argument("--q", type=float, nargs=2, default=[0.5, 0.5], metavar=("Q_G", "Q_A"))
     ap.add_argument("--dump-layers", default=None, help="write the per-layer conv timing table here")
-    ap.add_argument("--frames-per-step", type=int, default=6,
+    ap.add_argument("--frames-per-step", type=int, default=12,
                     help="frames coded per step per GPU (frame pipeline; 1 = one frame at a time)")
-    ap.add_argument("--depth", type=int, default=3, help="frames in flight per GPU")
+    ap.add_argument("--depth", type=int, default=4, help="frames in flight per GPU")
+    ap.add_argument("--scheduler", default="threads", choices=["threads", "cooperative"],
+                    help="frame pipeline: one launch thread per in-flight frame, or one thread resuming all frames")
     ap.add_argument("--no-tf32-pass", action="store_true",
                     help="skip the secondary tensor-core (tf32) measurement added to the exact-mode line")
     ap.add_argument("--scene", action="store_true",
@@ -238,7 +240,7 @@ def tf32_pass(args, model, dev, frame_dev, B, peaks, clocks):
     ops = pcc_b200.ops
     ops.set_default_mode(ops.MODE_TF32)
     try:
-        pipe = pcc_b200.pipeline.FramePipeline(model, depth=min(args.depth, B), device=dev)
+        pipe = pcc_b200.pipeline.FramePipeline(model, depth=min(args.depth, B), device=dev, scheduler=args.scheduler)
         import gc
         steps, warm = 3, 3
         for _ in range(warm):
@@ -412,7 +414,7 @@ def run_ours(args, rank, world, local_rank):
     frames = [frame_for(rank, s, world, args.radius, args.grid) for s in range(total * B if world > 1 else 1)]
     get = (lambda s: frames[s]) if world > 1 else (lambda s: frames[0])
     qmaps = {}
-    pipe = pcc_b200.pipeline.FramePipeline(model, depth=min(args.depth, B), device=dev)
+    pipe = pcc_b200.pipeline.FramePipeline(model, depth=min(args.depth, B), device=dev, scheduler=args.scheduler)
 
     def host_inputs(s):
         x = get(s)
@@ -467,7 +469,7 @@ def run_ours(args, rank, world, local_rank):
         tw = time.perf_counter()
         npts += step_device(s)
         step_wall.append(round((time.perf_counter() - tw) * 1e3, 2))
-        pipe_stats.append({k: round(v, 1) for k, v in pipe.stats.items()})
+        pipe_stats.append({k: (round(v, 1) if isinstance(v, float) else v) for k, v in pipe.stats.items()})
     ev1.record()  # the pipeline made this stream wait for every frame's stream
     barrier()
     t_dev = ev0.elapsed_time(ev1) * 1e-3
@@ -533,8 +535,9 @@ def run_ours(args, rank, world, local_rank):
                                f"voxelised shell frame, radius {args.radius:g} in a {args.grid}^3 grid -> {n_frame} points, RGB, "
                                f"uniform q=({args.q[0]:g},{args.q[1]:g}); in-memory variant (path=None)",
                    "mode": args.mode, "frames_per_step_per_gpu": B, "frames_in_flight_per_gpu": min(args.depth, B),
-                   "parallelism": f"frame-parallel x{world}, {min(args.depth, B)}-deep frame pipeline per GPU "
-                                  "(CPU range coder of one frame overlaps the kernels of the others)",
+                   "parallelism": f"frame-parallel x{world}, {min(args.depth, B)}-deep frame pipeline per GPU, scheduler "
+                                  f"'{args.scheduler}' (CPU range coder and count read-backs of one frame overlap the "
+                                  "kernels of the others)",
                    "l2": "per-step working set (>1 GB of activations and kernel maps) exceeds the 126 MB L2; no flush",
                    "includes_cpu_range_coder": True},
         "e2e": {"value": npts_all / t_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d // args.steps,

@@ -178,6 +178,17 @@ int pcc_conv_fwd(const pcc_conv_args* args, void* stream);
 /* One-off re-layout of a kernel for the tensor-core path: wt[k][co][ci] = tf32_round(w[k][ci][co]). */
 int pcc_weight_transpose(const float* w, int32_t K, int32_t cin, int32_t cout, float* wt, void* stream);
 
+/* Channel 0 of a convolution whose other output channels are never read — the occupancy head
+ * (model/blocks.py:142 reads F[:, 0] of occ_predict only) — in factorised form: P[i][k] =
+ * <in[i], weight[k][:, 0]> in one streaming pass, then out[order[j]] = bias[0] + sum_k P[nbr[k][j]][k],
+ * a 4-byte read per kernel-map pair instead of a cin-channel row.  fp32, but summed over ci before k:
+ * not the exact path's FMA order, so callers use it in the tolerance mode only.  Single-group kernel
+ * maps.  out [dev, n_out]; ws: pcc_conv_head0_ws_bytes(n_in). */
+size_t pcc_conv_head0_ws_bytes(int64_t n_in);
+int pcc_conv_head0(const float* in, int64_t n_in, int32_t cin, const float* weight, int32_t cout, const float* bias,
+                   const int32_t* nbr, int64_t nbr_stride, const int32_t* order, int64_t n_out, int32_t K,
+                   float* out, void* ws, size_t ws_bytes, void* stream);
+
 /* SparseTensor.features_at_coordinates for on-grid queries == gather-or-zero
  * (sites listed at pcc_hash_probe).  out[i] = rows[i] >= 0 ? in[rows[i]] : 0, optionally
  * out[i] = add[i] + that  (Q.F + Q_plus.features_at_coordinates(Q.C), model/transforms.py:96,262). */

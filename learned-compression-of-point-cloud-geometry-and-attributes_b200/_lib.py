@@ -61,6 +61,8 @@ SIGNATURES = {
     "pcc_kernel_map": (I32, [P, P, I64, P, I64, I32, I32, I32, P, I64, P, P, P, I64, I32, P, P, SZ, P]),
     "pcc_conv_fwd": (I32, [P, P]),
     "pcc_weight_transpose": (I32, [P, I32, I32, I32, P, P]),
+    "pcc_conv_head0_ws_bytes": (SZ, [I64]),
+    "pcc_conv_head0": (I32, [P, I64, I32, P, I32, P, P, I64, P, I64, I32, P, P, SZ, P]),
     "pcc_gather_rows": (I32, [P, I32, P, I64, P, P, P]),
     "pcc_topk_ws_bytes": (SZ, [I64]),
     "pcc_topk_select": (I32, [P, I64, I64, I64, P, P, SZ, P]),

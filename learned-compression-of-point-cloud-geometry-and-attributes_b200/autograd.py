@@ -24,8 +24,16 @@ class _SparseConv(torch.autograd.Function):
     @staticmethod
     def forward(ctx, feats, weight, bias, in_map, out_map, ksize, transpose):
         kmap = in_map.kernel_map(out_map, ksize, transpose=transpose)
-        out = ops.conv(feats, kmap, weight, bias, mode=ops.MODE_EXACT, round_out=False)
+        # precision policy of DESIGN.md §5: in the tensor-core mode the forward pass and the data gradient of
+        # layers with cin, cout % 32 == 0 run on tcgen05 (tf32 operands, fp32 accumulation); everything else,
+        # and the weight gradient, on the fp32 CUDA-core kernels
+        w3 = weight if weight.dim() == 3 else weight.unsqueeze(0)
+        mode = ops.default_mode()
+        if mode == ops.MODE_TF32 and not (ops.tf32_eligible(w3.shape[1], w3.shape[2]) and kmap.n_groups == 1):
+            mode = ops.MODE_EXACT
+        out = ops.conv(feats, kmap, weight, bias, mode=mode, round_out=False)
         ctx.save_for_backward(feats, weight)
+        ctx.mode = mode
         ctx.maps = (in_map, out_map, ksize, transpose, kmap)
         ctx.has_bias = bias is not None
         ctx.bias_shape = None if bias is None else tuple(bias.shape)
@@ -43,7 +51,8 @@ class _SparseConv(torch.autograd.Function):
             # nbr[k][o] = i  <=>  rnbr[k][i] = o: the same offsets probed from the other side
             rmap = out_map.kernel_map(in_map, ksize, transpose=not transpose)
             wt = w3.detach().transpose(1, 2).contiguous()
-            g_in = ops.conv(g, rmap, wt, None, mode=ops.MODE_EXACT, round_out=False)
+            mode = ctx.mode if (ctx.mode == ops.MODE_EXACT or rmap.n_groups == 1) else ops.MODE_EXACT
+            g_in = ops.conv(g, rmap, wt, None, mode=mode, round_out=False)
         if ctx.needs_input_grad[1]:
             g_w = ops.conv_wgrad(feats, g, kmap, cin, cout).view(weight.shape)
         if ctx.has_bias and ctx.needs_input_grad[2]:

@@ -204,10 +204,14 @@ class GenerativeUpBlock(nn.Module):
         other N_out - 1 output channels are not computed (4 kept for 16-byte alignment)."""
         last = self.occ_predict[2]
         ver = (last.kernel._version, last.kernel.data_ptr())
-        if self._head is None or self._head[0] != ver:
-            c = min(4, last.out_channels)
-            self._head = (ver, last.kernel.detach()[:, :, :c].contiguous(), last.bias.detach()[:, :c].contiguous())
-        return self._head[1], self._head[2]
+        head = self._head
+        if head is None or head[0] != ver:
+            with ops.cache_lock:
+                c = min(4, last.out_channels)
+                w, b = last.kernel.detach()[:, :, :c].contiguous(), last.bias.detach()[:, :c].contiguous()
+                ops.publish(w, b)
+                head = self._head = (ver, w, b)
+        return head[1], head[2]
 
     def _logits(self, x, full):
         t = apply_conv(x, self.occ_predict[0], act=RELU)
@@ -217,15 +221,22 @@ class GenerativeUpBlock(nn.Module):
         if last.training and AG.wants_grad(t.F, last.kernel):  # only channel 0 reaches the loss (loss.py:170)
             c = min(4, last.out_channels)
             return AG.sparse_conv(t.F, x.m, x.m, 3, last.kernel[:, :, :c], last.bias[:, :c])
+        kmap = x.m.kernel_map(x.m, 3)
+        if ops.default_mode() == ops.MODE_TF32 and kmap.n_groups == 1 and not isinstance(x.m, SlabMap):
+            # tolerance mode: project onto the 27 head vectors first, then gather scalars (pcc_conv_head0)
+            return ops.conv_head0(t.F, kmap, last.kernel.detach(), None if last.bias is None else last.bias.detach())
         w, b = self._occ_head()
-        return ops.conv(t.F, x.m.kernel_map(x.m, 3), w, b)
+        return ops.conv(t.F, kmap, w, b)
 
     @staticmethod
     def _topk(logits, cand_map, k):
         """_topk_prediction (:130-150): per batch id, the k largest logits of channel 0."""
         if isinstance(cand_map, SlabMap):  # scene-wide k over all slabs
             return cand_map.topk(logits, int(k[0]))
-        nb = int((cand_map.keys[-1] >> 48).item()) + 1 if cand_map.n else 0
+        if cand_map.n_batches is not None:
+            nb = cand_map.n_batches if cand_map.n else 0
+        else:
+            nb = int((cand_map.keys[-1] >> 48).item()) + 1 if cand_map.n else 0
         if nb <= 1:
             return ops.topk_rows(logits, int(k[0]))
         bounds = torch.searchsorted(cand_map.keys >> 48, torch.arange(nb + 1, device=logits.device)).tolist()
@@ -248,7 +259,7 @@ class GenerativeUpBlock(nn.Module):
         if isinstance(cand, SlabMap):
             up_map = cand.select(sel)
         else:
-            up_map = ops.CoordMap(ops.take_keys(cand.keys, sel), cand.ts, True)  # predictions.C[mask] (:164)
+            up_map = ops.CoordMap(ops.take_keys(cand.keys, sel), cand.ts, True, cand.n_batches)  # predictions.C[mask] (:164)
         x = ST(on_map(up_map, gather(x.F, sel)), up_map)                        # _prune_coords (:101-128)
         if not self.dense and self.condition_ablation is None:
             x = seq3(x, self.conv_2)
@@ -301,7 +312,7 @@ def _count_per_batch(m):
         return [m.count_total()]
     if m.n == 0:
         return []
-    nb = int((m.keys.max() >> 48).item()) + 1
+    nb = m.n_batches if m.n_batches is not None else int((m.keys.max() >> 48).item()) + 1
     if nb == 1:
         return [m.n]
     return torch.bincount((m.keys >> 48), minlength=nb).tolist()

@@ -292,16 +292,19 @@ class EntropyBottleneck(EntropyModel):
     def _device_params(self, device):
         """medians [C] and the 58 pre-transformed floats per channel the likelihood kernel reads."""
         key = str(device)
-        if key not in self._dev_cache:
-            with torch.no_grad():
-                parts = []
-                for i in range(5):
-                    parts.append(torch.nn.functional.softplus(getattr(self, f"_matrix{i}").double()).reshape(self.channels, -1))
-                    parts.append(getattr(self, f"_bias{i}").double().reshape(self.channels, -1))
-                    if i < 4:
-                        parts.append(torch.tanh(getattr(self, f"_factor{i}").double()).reshape(self.channels, -1))
-                packed = torch.cat(parts, dim=1).float().contiguous().to(device)
-                med = self.quantiles[:, 0, 1].detach().float().contiguous().to(device)
+        hit = self._dev_cache.get(key)
+        if hit is not None:
+            return hit
+        with ops.cache_lock, torch.no_grad():
+            parts = []
+            for i in range(5):
+                parts.append(torch.nn.functional.softplus(getattr(self, f"_matrix{i}").double()).reshape(self.channels, -1))
+                parts.append(getattr(self, f"_bias{i}").double().reshape(self.channels, -1))
+                if i < 4:
+                    parts.append(torch.tanh(getattr(self, f"_factor{i}").double()).reshape(self.channels, -1))
+            packed = torch.cat(parts, dim=1).float().contiguous().to(device)
+            med = self.quantiles[:, 0, 1].detach().float().contiguous().to(device)
+            ops.publish(med, packed)
             self._dev_cache[key] = (med, packed)
         return self._dev_cache[key]
 
@@ -411,9 +414,13 @@ class GaussianConditional(EntropyModel):
 
     def _table_dev(self, device):
         key = str(device)
-        if key not in self._dev_cache:
-            self._dev_cache[key] = self.scale_table.detach().float().contiguous().to(device)
-        return self._dev_cache[key]
+        hit = self._dev_cache.get(key)
+        if hit is None:
+            with ops.cache_lock:
+                hit = self.scale_table.detach().float().contiguous().to(device)
+                ops.publish(hit)
+                self._dev_cache[key] = hit
+        return hit
 
     @staticmethod
     def _params(scales, means):

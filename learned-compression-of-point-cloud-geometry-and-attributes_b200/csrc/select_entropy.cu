@@ -39,6 +39,58 @@ __global__ void gather_rows_kernel(const float* __restrict__ in, int c, const in
   }
 }
 
+// ---------------------------------------------------------------- occupancy head, factorised form
+// Channel 0 of a convolution whose other output channels nobody reads (the occupancy head,
+// model/blocks.py:142): out[o] = b0 + sum_k <in[nbr[k][o]], W[k][:, 0]>.  Gathering 64-128-channel rows
+// for ONE output channel makes the direct kernel gather-bound (19 GB of rows per 4 M-candidate
+// layer); projecting first, P[i][k] = <in[i], W[k][:, 0]> (one streaming pass, 32 floats per row),
+// turns the gather into one 4-byte read per pair.  fp32 throughout, but the sum over ci is taken
+// before the sum over k — a different rounding order than the exact path's single (k, ci) FMA
+// chain, so this form serves the tolerance mode (PCC_MODE_TF32) only.
+constexpr int HP_ROWS = 64;   // rows per block
+constexpr int HP_K = 32;      // padded offsets per row of P
+
+__global__ void __launch_bounds__(256)
+head_project_kernel(const float* __restrict__ in, int64_t n, int cin, const float* __restrict__ w, int K, int cout,
+                    float* __restrict__ P) {
+  extern __shared__ float hp_smem[];
+  float* w_s = hp_smem;                 // [cin][HP_K]
+  float* x_s = hp_smem + cin * HP_K;    // [HP_ROWS][cin + 1]
+  const int tid = threadIdx.x;
+  for (int e = tid; e < cin * HP_K; e += 256) {
+    const int ci = e / HP_K, k = e % HP_K;
+    w_s[e] = k < K ? __ldg(w + ((int64_t)k * cin + ci) * cout) : 0.f;
+  }
+  const int64_t r0 = (int64_t)blockIdx.x * HP_ROWS;
+  for (int e = tid; e < HP_ROWS * cin; e += 256) {
+    const int r = e / cin, c = e % cin;
+    x_s[r * (cin + 1) + c] = r0 + r < n ? __ldg(in + (r0 + r) * cin + c) : 0.f;
+  }
+  __syncthreads();
+  const int k = tid % HP_K;
+  for (int r = tid / HP_K; r < HP_ROWS; r += 256 / HP_K) {
+    if (r0 + r >= n) break;
+    float acc = 0.f;
+    const float* xr = x_s + r * (cin + 1);
+#pragma unroll 8
+    for (int ci = 0; ci < cin; ++ci) acc = fmaf(xr[ci], w_s[ci * HP_K + k], acc);
+    P[(r0 + r) * HP_K + k] = acc;
+  }
+}
+
+__global__ void head_gather_kernel(const float* __restrict__ P, const int32_t* __restrict__ nbr, int64_t nbr_stride,
+                                   const int32_t* __restrict__ order, int64_t n_out, int K,
+                                   const float* __restrict__ bias, float* __restrict__ out) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n_out) return;
+  float acc = bias ? __ldg(bias) : 0.f;
+  for (int k = 0; k < K; ++k) {
+    const int32_t i = __ldg(nbr + (int64_t)k * nbr_stride + j);
+    if (i >= 0) acc += __ldg(P + (int64_t)i * HP_K + k);
+  }
+  out[order ? (int64_t)__ldg(order + j) : j] = acc;
+}
+
 // ---------------------------------------------------------------- top-k radix select
 __device__ __forceinline__ uint32_t float_key(float f) {
   const uint32_t u = __float_as_uint(f);
@@ -377,6 +429,31 @@ static dim3 tile_grid(int64_t n, int c) { return dim3((unsigned)ceil_div(n, ET),
 using namespace pcc;
 
 extern "C" {
+
+size_t pcc_conv_head0_ws_bytes(int64_t n_in) { return (size_t)(n_in > 0 ? n_in : 1) * HP_K * sizeof(float); }
+
+int pcc_conv_head0(const float* in, int64_t n_in, int32_t cin, const float* weight, int32_t cout, const float* bias,
+                   const int32_t* nbr, int64_t nbr_stride, const int32_t* order, int64_t n_out, int32_t K,
+                   float* out, void* ws, size_t ws_bytes, void* stream) {
+  if (n_out == 0) return PCC_OK;
+  PCC_REQUIRE(in && weight && nbr && out && ws, "null pointer");
+  PCC_REQUIRE(cin > 0 && cout > 0 && K > 0 && K <= 27 && nbr_stride >= n_out, "bad shape");
+  PCC_REQUIRE(ws_bytes >= pcc_conv_head0_ws_bytes(n_in), "workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  float* P = reinterpret_cast<float*>(ws);
+  const size_t smem = ((size_t)cin * HP_K + (size_t)HP_ROWS * (cin + 1)) * sizeof(float);
+  PCC_REQUIRE(smem <= 96 * 1024, "cin too large for the projection tile");
+  static bool attr_done = false;
+  if (!attr_done) {
+    PCC_CHECK_CUDA(cudaFuncSetAttribute(head_project_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    attr_done = true;
+  }
+  head_project_kernel<<<(unsigned)ceil_div(n_in, HP_ROWS), 256, smem, st>>>(in, n_in, cin, weight, K, cout, P);
+  PCC_CHECK_LAUNCH("head_project_kernel");
+  head_gather_kernel<<<grid_for(n_out), THREADS, 0, st>>>(P, nbr, nbr_stride, order, n_out, K, bias, out);
+  PCC_CHECK_LAUNCH("head_gather_kernel");
+  return PCC_OK;
+}
 
 int pcc_gather_rows(const float* in, int32_t c, const int32_t* rows, int64_t n, const float* add,
                     float* out, void* stream) {

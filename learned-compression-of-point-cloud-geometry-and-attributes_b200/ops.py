@@ -5,6 +5,7 @@ libpcc_b200.so.  There is no CPU fallback: tensors must live on a CUDA device.
 """
 import ctypes
 import os
+import threading
 import weakref
 
 import torch
@@ -18,6 +19,8 @@ MODE_EXACT, MODE_TF32 = 0, 1
 LEAKY_SLOPE = 0.01  # ME.MinkowskiLeakyReLU default
 
 _launches = 0  # kernels enqueued through this module (bench.py reports it as gpu_launches)
+_count_lock = threading.Lock()
+cache_lock = threading.RLock()  # guards the creation of device tensors cached across frames / threads
 
 
 def launches():
@@ -26,7 +29,15 @@ def launches():
 
 def _count(n=1):
     global _launches
-    _launches += n
+    with _count_lock:  # frames are launched from several threads (pipeline.FramePipeline)
+        _launches += n
+
+
+def publish(*tensors):
+    """A device tensor about to be cached and read from OTHER streams (frame threads each have their own):
+    wait until the current stream has produced it.  One-off per cache entry."""
+    torch.cuda.current_stream().synchronize()
+    return tensors[0] if len(tensors) == 1 else tensors
 
 
 def _L():
@@ -122,10 +133,14 @@ class CoordMap:
     layers that share coordinates share maps.
     """
 
-    def __init__(self, keys, ts, is_sorted):
+    def __init__(self, keys, ts, is_sorted, n_batches=None):
         self.keys = keys
         self.ts = int(ts)
         self.is_sorted = bool(is_sorted)
+        # upper bound of (largest batch id + 1) when known on the host: read once where the coordinates
+        # enter (canonical_map) and inherited by every derived map, so that per-batch logic (point
+        # counts, per-batch top-k) never has to synchronise the stream to ask the device
+        self.n_batches = None if n_batches is None else int(n_batches)
         self._hash = None
         self._coords = None
         self._derived = {}
@@ -179,7 +194,7 @@ class CoordMap:
                                          _ptr(ws), wsb, _stream()), "pcc_coords_stride")
             _count(8)
             self._derived["s2"] = CoordMap(out[:n_out.value].clone() if n_out.value < n else out[:n_out.value],
-                                           self.ts * 2, True)
+                                           self.ts * 2, True, self.n_batches)
         return self._derived["s2"]
 
     def expand(self, kernel_size):
@@ -197,7 +212,7 @@ class CoordMap:
                                          _ptr(out), ctypes.byref(n_out), _ptr(ws), wsb, _stream()),
                   "pcc_coords_expand")
             _count(8)
-            self._derived[key] = CoordMap(out[:n_out.value].clone(), self.ts // 2, True)
+            self._derived[key] = CoordMap(out[:n_out.value].clone(), self.ts // 2, True, self.n_batches)
         return self._derived[key]
 
     def kernel_map(self, out_map, kernel_size, transpose=False, groups=None):
@@ -311,12 +326,13 @@ def canonical_map(coords, ts=1):
     keys, status = pack_coords(coords)
     skeys, perm = sort_keys(keys)
     dup = (skeys[1:] == skeys[:-1]).any() if skeys.shape[0] > 1 else torch.zeros((), dtype=torch.bool, device=keys.device)
-    flags = torch.stack([status[0] != 0, dup.reshape(())]).tolist()
+    last_batch = (skeys[-1] >> 48) if skeys.shape[0] else torch.zeros((), dtype=torch.int64, device=keys.device)
+    flags = torch.stack([(status[0] != 0).long(), dup.reshape(()).long(), last_batch.reshape(()).long()]).tolist()
     if flags[0]:
         raise _lib.PccError("coordinate out of the packable range (|x|,|y|,|z| < 32768, 0 <= b < 65536)")
     if flags[1]:
         raise _lib.PccError("duplicate coordinates")
-    return CoordMap(skeys, ts, True), perm.long()
+    return CoordMap(skeys, ts, True, flags[2] + 1 if skeys.shape[0] else 0), perm.long()
 
 
 # ---------------------------------------------------------------------------- convolution
@@ -376,6 +392,15 @@ def transposed_weight(weight):
     hit = _wt_cache.get(key)
     if hit is not None and hit[0]() is weight and hit[1] == ver:
         return hit[2]
+    with cache_lock:
+        return _transposed_weight_build(weight, key, ver)
+
+
+def _transposed_weight_build(weight, key, ver):
+    import weakref
+    hit = _wt_cache.get(key)
+    if hit is not None and hit[0]() is weight and hit[1] == ver:
+        return hit[2]
     if len(_wt_cache) > 512:
         for k in [k for k, v in _wt_cache.items() if v[0]() is None]:
             del _wt_cache[k]
@@ -385,6 +410,7 @@ def transposed_weight(weight):
     wt = torch.empty((K, cout, cin), dtype=torch.float32, device=w.device)
     check(_L().pcc_weight_transpose(_ptr(w), K, cin, cout, _ptr(wt), _stream()), "pcc_weight_transpose")
     _count()
+    publish(wt)
     _wt_cache[key] = (weakref.ref(weight), ver, wt)
     return wt
 
@@ -471,6 +497,26 @@ def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None
     check(_L().pcc_conv_fwd(ctypes.byref(a), _stream()), "pcc_conv_fwd")
     if n_out:
         _count(kmap.n_groups)
+    return out
+
+
+def conv_head0(feats, kmap, weight, bias=None):
+    """Channel 0 of conv(feats, kmap, weight, bias) in factorised form -> [n_out, 1]
+    (pcc_conv_head0: tolerance mode only; single-group kernel maps)."""
+    _need_cuda(feats, "feats")
+    feats = feats.contiguous()
+    w = (weight if weight.dim() == 3 else weight.unsqueeze(0)).contiguous()
+    K, cin, cout = w.shape
+    if K != kmap.K or feats.shape[1] != cin or kmap.n_groups > 1:
+        raise _lib.PccError("conv_head0: shape mismatch or multi-group kernel map")
+    out = torch.empty((kmap.n_out, 1), dtype=torch.float32, device=feats.device)
+    wsb = _L().pcc_conv_head0_ws_bytes(feats.shape[0])
+    ws = _ws(wsb, feats.device)
+    b = None if bias is None else bias.contiguous()
+    check(_L().pcc_conv_head0(_ptr(feats), feats.shape[0], cin, _ptr(w), cout, _ptr(b), _ptr(kmap.nbr), kmap.stride,
+                              _ptr(kmap.order), kmap.n_out, K, _ptr(out), _ptr(ws), wsb, _stream()), "pcc_conv_head0")
+    if kmap.n_out:
+        _count(2)
     return out
 
 

@@ -116,10 +116,11 @@ def test_me_surface_matches_fused_path(pcc):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("scheduler", ["threads", "cooperative"])
 @pytest.mark.parametrize("host_io", [False, True])
-def test_frame_pipeline_matches_sequential(pcc, host_io):
-    """Several frames in flight (cooperative scheduler, coder threads) give byte-identical strings and
-    bit-identical clouds to coding the frames one at a time."""
+def test_frame_pipeline_matches_sequential(pcc, host_io, scheduler):
+    """Several frames in flight (one launch thread per frame, or the cooperative single-thread scheduler;
+    coder threads) give byte-identical strings and bit-identical clouds to coding the frames one at a time."""
     dev = "cuda:0"
     model = pcc.ColorModel(pcc.OURS_CONFIG)
     pcc.init_synthetic(model, 0)
@@ -135,7 +136,7 @@ def test_frame_pipeline_matches_sequential(pcc, host_io):
     for x, Q in frames:
         s, sh, k, c = model.compress(x, Q)
         seq.append((model.decompress(coordinates=c, strings=s, shape=sh, k=k), s, c))
-    pipe = pcc.pipeline.FramePipeline(model, depth=3, device=dev)
+    pipe = pcc.pipeline.FramePipeline(model, depth=3, device=dev, scheduler=scheduler)
     for _ in range(2):
         got = pipe.roundtrip_many(frames, host_io=host_io)
         torch.cuda.synchronize()

@@ -121,3 +121,26 @@ def test_codec_tf32_roundtrip_and_tolerance(pcc):
     # a 1e-3 perturbation reorders many voxels at the three cascaded top-k thresholds (measured 0.54
     # on this frame).  The bit-exact occupancy claim belongs to the exact mode (test_gpu_codec.py).
     assert iou > 0.25, iou
+
+
+@pytest.mark.parametrize("cin", [64, 128, 20])
+def test_factorised_head_matches_direct_convolution(pcc, cin):
+    """pcc_conv_head0 (projection, then a scalar gather) == channel 0 of the exact convolution up to the
+    fp32 summation order: max error 1e-5 of the largest logit."""
+    import numpy as np
+    from conftest import random_cloud
+    rng = np.random.default_rng(cin)
+    c = random_cloud(5000, 24, cin, 2, 0)
+    m, _ = pcc.ops.canonical_map(torch.from_numpy(c).to("cuda:0"), 1)
+    x = torch.from_numpy(rng.standard_normal((m.n, cin)).astype(np.float32)).to("cuda:0")
+    W = torch.from_numpy((rng.standard_normal((27, cin, 7)) / np.sqrt(cin * 9)).astype(np.float32)).to("cuda:0")
+    b = torch.from_numpy(rng.standard_normal((1, 7)).astype(np.float32)).to("cuda:0")
+    pcc.ops.set_tap_groups(1)
+    try:
+        km = m.kernel_map(m, 3)
+        ref = pcc.ops.conv(x, km, W, b, mode=pcc.ops.MODE_EXACT)[:, 0]
+        got = pcc.ops.conv_head0(x, km, W, b)[:, 0]
+    finally:
+        pcc.ops.set_tap_groups(None)
+    err = (got - ref).abs().max().item() / ref.abs().max().item()
+    assert err <= 1e-5, err

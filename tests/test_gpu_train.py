@@ -330,3 +330,44 @@ def test_me_shaped_modules_are_differentiable(pcc):
         _close(a, b, what=f"kernel gradient {i}")
     for i, (a, b) in enumerate(zip(bg, bc)):
         _close(a, b, what=f"bias gradient {i}")
+
+
+def test_training_step_in_tensor_core_mode(pcc):
+    """tf32 mode: forward and data gradient of the wide layers on tcgen05.  Loss within 2 %; gradient tensors
+    against the fp32 path's: median cosine >= 0.995, none below 0.9 (tolerance mode: 10-bit operands through
+    ~60 layers, and top-k may flip single voxels)."""
+    g = np.load(TRAIN_GOLDEN[0])
+    x, Q, Lambda = _golden_batch(pcc, g)
+    noise = [torch.from_numpy(g[f"noise{i}"]) for i in range(int(g["n_noise"]))]
+    grads, totals = [], []
+    for mode in (pcc.ops.MODE_EXACT, pcc.ops.MODE_TF32):
+        pcc.ops.set_default_mode(mode)
+        try:
+            model = pcc.ColorModel(getattr(pcc, str(g["config"])))
+            pcc.init_synthetic(model, int(g["wseed"]))
+            model.to(DEV).train()
+            it = iter(noise)
+
+            def replay(like):
+                n = next(it)
+                if tuple(n.shape) != tuple(like.shape):
+                    n = n[0].t() if n.shape[0] == 1 else n.reshape(like.shape)
+                return n.contiguous()
+
+            pcc.compressai_compat.set_noise_source(replay)
+            total, _ = pcc.loss.Loss(LOSS_CONFIG)(x, model(x, Q, Lambda))
+            total.backward()
+            totals.append(float(total.detach()))
+            grads.append({n: p.grad.detach().flatten().double() for n, p in model.named_parameters() if p.grad is not None})
+        finally:
+            pcc.compressai_compat.set_noise_source(None)
+            pcc.ops.set_default_mode(pcc.ops.MODE_EXACT)
+    assert abs(totals[1] - totals[0]) <= 2e-2 * abs(totals[0]), totals
+    cos = []
+    for n, a in grads[0].items():
+        b = grads[1][n]
+        if a.numel() >= 1024 and a.norm() > 0:
+            cos.append((float((a @ b) / (a.norm() * b.norm())), n))
+    cos.sort()
+    print("lowest cosines:", cos[:4], "median", cos[len(cos) // 2][0])
+    assert cos[len(cos) // 2][0] >= 0.995 and cos[0][0] >= 0.9, cos[:6]

@@ -37,9 +37,12 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--layers", default=None)
+    ap.add_argument("--mode", default="exact", choices=["exact", "tf32"],
+                    help="tf32: forward and data gradient of the >= 32-channel layers on tcgen05 (weight gradient fp32)")
     a = ap.parse_args()
     import pcc_b200 as pcc
     dev = "cuda:0"
+    pcc.ops.set_default_mode(pcc.ops.MODE_TF32 if a.mode == "tf32" else pcc.ops.MODE_EXACT)
     model = pcc.ColorModel(pcc.OURS_CONFIG)
     pcc.init_synthetic(model, 0)
     model.to(dev).train()
@@ -105,6 +108,7 @@ def main():
     step()
     recs = pcc.ops.stop_conv_profile()
     big = [r for r in recs if r["mode"] == -1 and r["cin"] >= 64 and r["cout"] >= 64]
+    tc = [r for r in recs if r["mode"] == 1 and r["cin"] >= 64 and r["cout"] >= 64]
     wg_all = sum(r["ms"] for r in recs if r["mode"] == -1)
     conv_all = sum(r["ms"] for r in recs if r["mode"] != -1)
     flops = sum(2.0 * r["pairs"] * r["cin"] * r["cout"] for r in big)
@@ -122,12 +126,16 @@ def main():
         "metric": "training step points/sec (forward + loss + backward + Adam)", "value": n / (total_ms / 1e3),
         "unit": "points/s", "ms_per_step": total_ms, "points_per_batch": n, "batch": a.batch,
         "phases_ms": {"forward+loss": fwd, "backward": bwd, "clip+adam+aux": opt_ms},
-        "gpu_launches_per_step": launches / a.steps, "last_loss": loss, "dtype": "f32",
+        "gpu_launches_per_step": launches / a.steps, "last_loss": loss, "dtype": "f32" if a.mode == "exact" else "tf32",
+        "tensor_core_conv": None if not tc else {
+            "kernel": "conv_tf32_kernel (forward + data gradient)", "launches": len(tc),
+            "achieved": sum(2.0 * r["pairs"] * r["cin"] * r["cout"] for r in tc) / sum(r["ms"] for r in tc) / 1e9,
+            "unit": "TFLOP/s"},
         "conv_ms_per_step": {"forward+data-gradient (pcc_conv_fwd)": conv_all, "weight-gradient (pcc_conv_wgrad)": wg_all},
         "roofline": {"bound": "fp32_fma", "kernel": "conv_wgrad_kernel", "achieved": flops / max(ms, 1e-9) / 1e9,
                      "peak": peak, "unit": "TFLOP/s", "frac": flops / max(ms, 1e-9) / 1e9 / peak,
                      "launches": len(big), "peak_source": "148 SM x 128 FMA x 2 x 1965 MHz"},
-        "config": {"workload": f"Ours.yaml random-init, batch of {a.batch} synthetic 7-bit shell blocks (radius "
+        "config": {"mode": a.mode, "workload": f"Ours.yaml random-init, batch of {a.batch} synthetic 7-bit shell blocks (radius "
                                f"{a.radius}..{a.radius - a.batch + 1} in 128^3), loss section of configs/Ours.yaml"}}))
 
 
