@@ -264,6 +264,9 @@ typedef struct pcc_wgrad_args {
   float* dweight;           /* [dev, K x cin x cout] receives the gradient (overwritten) */
   void* ws;
   size_t ws_bytes;
+  int32_t mode;             /* PCC_MODE_EXACT: fp32 CUDA cores; PCC_MODE_TF32: tcgen05 (tf32 operands, fp32
+                             * accumulation in TMEM) when cin, cout % 32 == 0 and cout <= 256, else fp32 */
+  int32_t reserved;         /* 0 */
 } pcc_wgrad_args;
 size_t pcc_conv_wgrad_ws_bytes(int32_t K, int32_t cin, int32_t cout);
 int pcc_conv_wgrad(const pcc_wgrad_args* args, void* stream);

@@ -37,7 +37,7 @@ class WgradArgs(ctypes.Structure):
     _fields_ = [
         ("in_", P), ("gout", P), ("cin", I32), ("cout", I32), ("nbr", P), ("nbr_stride", I64),
         ("tapmask", P), ("order", P), ("n_out", I64), ("K", I32), ("n_groups", I32),
-        ("dweight", P), ("ws", P), ("ws_bytes", SZ),
+        ("dweight", P), ("ws", P), ("ws_bytes", SZ), ("mode", I32), ("reserved", I32),
     ]
 
 

@@ -25,8 +25,8 @@ class _SparseConv(torch.autograd.Function):
     def forward(ctx, feats, weight, bias, in_map, out_map, ksize, transpose):
         kmap = in_map.kernel_map(out_map, ksize, transpose=transpose)
         # precision policy of DESIGN.md §5: in the tensor-core mode the forward pass and the data gradient of
-        # layers with cin, cout % 32 == 0 run on tcgen05 (tf32 operands, fp32 accumulation); everything else,
-        # and the weight gradient, on the fp32 CUDA-core kernels
+        # layers with cin, cout % 32 == 0 run on tcgen05 (tf32 operands, fp32 accumulation), and so does their
+        # weight gradient; everything else on the fp32 CUDA-core kernels
         w3 = weight if weight.dim() == 3 else weight.unsqueeze(0)
         mode = ops.default_mode()
         if mode == ops.MODE_TF32 and not (ops.tf32_eligible(w3.shape[1], w3.shape[2]) and kmap.n_groups == 1):
@@ -54,7 +54,7 @@ class _SparseConv(torch.autograd.Function):
             mode = ctx.mode if (ctx.mode == ops.MODE_EXACT or rmap.n_groups == 1) else ops.MODE_EXACT
             g_in = ops.conv(g, rmap, wt, None, mode=mode, round_out=False)
         if ctx.needs_input_grad[1]:
-            g_w = ops.conv_wgrad(feats, g, kmap, cin, cout).view(weight.shape)
+            g_w = ops.conv_wgrad(feats, g, kmap, cin, cout, mode=ctx.mode).view(weight.shape)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             g_b = g.sum(dim=0).view(ctx.bias_shape)
         return g_in, g_w, g_b, None, None, None, None

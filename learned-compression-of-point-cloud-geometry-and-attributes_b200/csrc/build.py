@@ -14,7 +14,7 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 CUFLAGS = ARCH + ["-O3", "-std=c++17", "-lineinfo", "-ccbin", CCBIN, "-Xcompiler", "-fPIC,-O3",
                   "--expt-relaxed-constexpr", "-Xptxas", "-v"]
 SOURCES = ["common.cu", "coords.cu", "conv_exact.cu", "conv_tf32.cu", "conv_dispatch.cu",
-           "select_entropy.cu", "octree.cu", "train.cu", "host_coder.cpp"]
+           "select_entropy.cu", "octree.cu", "train.cu", "wgrad_tf32.cu", "host_coder.cpp"]
 HEADERS = ["pcc_common.cuh", os.path.join("..", "..", "include", "pcc_b200.h")]
 
 

@@ -317,6 +317,11 @@ __global__ void gc_train_bwd_kernel(const float* __restrict__ yt, const float* _
 
 }  // namespace pcc
 
+namespace pcc {
+bool wgrad_tf32_supported(const pcc_wgrad_args* a);
+int wgrad_tf32(const pcc_wgrad_args* a, int* splits, cudaStream_t st);
+}  // namespace pcc
+
 using namespace pcc;
 
 extern "C" {
@@ -340,6 +345,15 @@ int pcc_conv_wgrad(const pcc_wgrad_args* a, void* stream) {
   PCC_REQUIRE(a->nbr_stride >= a->n_out, "nbr_stride < n_out");
   PCC_REQUIRE(a->ws_bytes >= pcc_conv_wgrad_ws_bytes(a->K, a->cin, a->cout), "workspace too small");
   PCC_REQUIRE(a->n_groups <= 1 || (a->order && a->n_groups <= a->K), "n_groups > 1 needs order and n_groups <= K");
+  if (a->mode == PCC_MODE_TF32 && wgrad_tf32_supported(a)) {
+    int splits = 1;
+    const int rc = wgrad_tf32(a, &splits, st);
+    if (rc != PCC_OK) return rc;
+    wgrad_reduce_kernel<<<(unsigned)ceil_div(wn, 256), 256, 0, st>>>(reinterpret_cast<const float*>(a->ws), splits, wn,
+                                                                   a->dweight);
+    PCC_CHECK_LAUNCH("wgrad_reduce_kernel");
+    return PCC_OK;
+  }
   const Side sa = side_for(a->cin), sb = side_for(a->cout);
   const int zt = (int)(ceil_div(a->cin, sa.t * sa.n) * ceil_div(a->cout, sb.t * sb.n));
   WgradParams p;

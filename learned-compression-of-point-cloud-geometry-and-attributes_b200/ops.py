@@ -534,7 +534,7 @@ def gather_rows(feats, rows, add=None):
     return out
 
 
-def conv_wgrad(feats, gout, kmap, cin, cout):
+def conv_wgrad(feats, gout, kmap, cin, cout, mode=MODE_EXACT):
     """Weight gradient of conv(): dW[k] = sum_j feats[nbr[k][j]]^T (x) gout[order[j]]  -> [K, cin, cout].
     Deterministic (fixed summation order).  SURVEY.md §8f row 4; ME ConvolutionBackward's grad_kernel."""
     _need_cuda(feats, "feats")
@@ -553,9 +553,11 @@ def conv_wgrad(feats, gout, kmap, cin, cout):
     a.order = None if kmap.order is None else kmap.order.data_ptr()
     a.n_out, a.K, a.n_groups = kmap.n_out, K, kmap.n_groups
     a.dweight, a.ws, a.ws_bytes = dw.data_ptr(), ws.data_ptr(), wsb
+    a.mode = int(mode)
     if _profile is not None and kmap.n_out:
         rec = {"cin": cin, "cout": cout, "K": K, "n_in": int(feats.shape[0]), "n_out": int(kmap.n_out),
-               "pairs": _pairs(kmap), "mode": -1, "ev0": torch.cuda.Event(enable_timing=True),
+               "pairs": _pairs(kmap), "mode": -1 if not (mode == MODE_TF32 and tf32_eligible(cin, cout)) else -2,
+               "ev0": torch.cuda.Event(enable_timing=True),
                "ev1": torch.cuda.Event(enable_timing=True)}
         rec["ev0"].record()
         check(_L().pcc_conv_wgrad(ctypes.byref(a), _stream()), "pcc_conv_wgrad")

@@ -371,3 +371,25 @@ def test_training_step_in_tensor_core_mode(pcc):
     cos.sort()
     print("lowest cosines:", cos[:4], "median", cos[len(cos) // 2][0])
     assert cos[len(cos) // 2][0] >= 0.995 and cos[0][0] >= 0.9, cos[:6]
+
+
+@pytest.mark.parametrize("cin,cout,ks,stride,transpose,groups", [
+    (128, 128, 3, 1, False, 1), (64, 64, 3, 1, False, 3), (128, 256, 3, 1, False, None), (192, 256, 3, 1, False, None),
+    (64, 32, 3, 1, False, None), (128, 192, 2, 2, True, None), (64, 128, 3, 2, False, None), (32, 32, 1, 1, False, None)])
+def test_tensor_core_weight_gradient(pcc, oracle, cin, cout, ks, stride, transpose, groups):
+    """wgrad_tf32_kernel (tcgen05, MN-major gathered operands) against the fp32 weight gradient: operands are
+    truncated to tf32 (10-bit mantissa), accumulation is fp32: within 2e-3 of the largest entry; deterministic."""
+    rng = np.random.default_rng(cin + 3 * cout + ks)
+    pcc.ops.set_tap_groups(groups)
+    try:
+        m, out_map, _ = _maps(pcc, oracle, 4000, 24, 4, cin + cout + 1, ks, stride, transpose)
+        km = m.kernel_map(out_map, ks, transpose=transpose)
+        x = torch.from_numpy(rng.standard_normal((m.n, cin)).astype(np.float32)).to(DEV)
+        G = torch.from_numpy(rng.standard_normal((out_map.n, cout)).astype(np.float32)).to(DEV)
+        ref = pcc.ops.conv_wgrad(x, G, km, cin, cout, mode=pcc.ops.MODE_EXACT)
+        got = pcc.ops.conv_wgrad(x, G, km, cin, cout, mode=pcc.ops.MODE_TF32)
+        again = pcc.ops.conv_wgrad(x, G, km, cin, cout, mode=pcc.ops.MODE_TF32)
+    finally:
+        pcc.ops.set_tap_groups(None)
+    assert torch.equal(got, again)
+    _close(got.cpu().numpy(), ref.cpu().numpy(), 2e-3, "tensor-core weight gradient")
