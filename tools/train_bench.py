@@ -115,6 +115,12 @@ def main():
     flops = sum(2.0 * r["pairs"] * r["cin"] * r["cout"] for r in big)
     ms = sum(r["ms"] for r in big)
     peak = 148 * 128 * 2 * 1.965e9 / 1e12
+    try:
+        tc_peak = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                              "MEASURED_PEAKS.json")))["bf16_tflops"] / 2.0
+        tc_src = "tf32 dense = measured bf16 burst / 2 (MEASURED_PEAKS.json)"
+    except (OSError, KeyError, ValueError):
+        tc_peak, tc_src = 1590.0 / 2.0, "fallback 1590/2"
     if a.layers:
         with open(a.layers, "w") as f:
             f.write("kind,cin,cout,K,n_in,n_out,pairs,ms,tflops\n")
@@ -137,8 +143,8 @@ def main():
                       "peak": peak, "unit": "TFLOP/s", "frac": flops / max(ms, 1e-9) / 1e9 / peak,
                       "launches": len(big), "peak_source": "148 SM x 128 FMA x 2 x 1965 MHz"} if not wg_tc else
                      {"bound": "tensor", "kernel": "wgrad_tf32_kernel", "achieved": flops / max(ms, 1e-9) / 1e9,
-                      "peak": 772.1, "unit": "TFLOP/s", "frac": flops / max(ms, 1e-9) / 1e9 / 772.1,
-                      "launches": len(big), "peak_source": "tf32 dense = measured bf16 burst / 2 (MEASURED_PEAKS.json)"}),
+                      "peak": tc_peak, "unit": "TFLOP/s", "frac": flops / max(ms, 1e-9) / 1e9 / tc_peak,
+                      "launches": len(big), "peak_source": tc_src}),
         "config": {"mode": a.mode, "workload": f"Ours.yaml random-init, batch of {a.batch} synthetic 7-bit shell blocks (radius "
                                f"{a.radius}..{a.radius - a.batch + 1} in 128^3), loss section of configs/Ours.yaml"}}))
 
