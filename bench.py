@@ -45,8 +45,9 @@ def parse_args():
     ap.add_argument("--frames-per-step", type=int, default=12,
                     help="frames coded per step per GPU (frame pipeline; 1 = one frame at a time)")
     ap.add_argument("--depth", type=int, default=4, help="frames in flight per GPU")
-    ap.add_argument("--scheduler", default="threads", choices=["threads", "cooperative"],
-                    help="frame pipeline: one launch thread per in-flight frame, or one thread resuming all frames")
+    ap.add_argument("--scheduler", default="auto", choices=["auto", "threads", "cooperative"],
+                    help="frame pipeline: one launch thread per in-flight frame, or one thread resuming all frames; "
+                         "auto = threads when this rank's share of the host cores covers its launch and coder threads")
     ap.add_argument("--no-tf32-pass", action="store_true",
                     help="skip the secondary tensor-core (tf32) measurement added to the exact-mode line")
     ap.add_argument("--scene", action="store_true",
@@ -400,6 +401,11 @@ def run_ours(args, rank, world, local_rank):
     dev = torch.device(f"cuda:{local_rank}")
     torch.cuda.set_device(dev)
     ops.set_default_mode(ops.MODE_TF32 if args.mode == "tf32" else ops.MODE_EXACT)
+    if args.scheduler == "auto":
+        # every launch thread spins in its CUDA waits: with fewer host cores per rank than in-flight frames plus
+        # a coder thread the threads would fight each other, and the single-thread scheduler is the better one
+        cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        args.scheduler = "threads" if cores // max(1, world) >= args.depth + 1 else "cooperative"
     model, cfg = make_model(args.config, dev)
     peaks = {}
     try:

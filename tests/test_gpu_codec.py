@@ -67,6 +67,55 @@ def test_decompress_accepts_float_unsorted_coordinates(pcc, oracle):
     assert torch.equal(a, b)
 
 
+def test_prune_before_refine_variant_bit_exact(pcc, oracle):
+    """g_s.dense = False (model/transforms.py:160-163, model/blocks.py:156-175): occupancy is predicted and
+    pruned before conv_2.  No shipped config sets it; the switch is on the path."""
+    import copy
+    config = copy.deepcopy(pcc.OURS_CONFIG)
+    config["g_s"]["dense"] = False
+    model, oc, got, ref, x = _run(pcc, oracle, config, 19.0, 11)
+    strings, shape, k, coords = got
+    o_strings, o_shape, o_k, o_coords = ref
+    assert strings == o_strings and shape == o_shape and k == o_k
+    out = model.decompress(coordinates=coords, strings=strings, shape=shape, k=k)
+    o_out = oc.decompress(o_coords, o_strings, o_shape, o_k)
+    assert np.array_equal(out.cpu().numpy(), o_out)
+
+
+def test_two_hyperprior_variant_round_trip(pcc):
+    """``entropy_model_map`` in the config (model/model.py:22-27,131-135,196-200): y and the latent quality
+    map are coded by two independent MeanScaleHyperprior models (model/entropy_models.py:104-250).  No
+    shipped config selects it and the oracle does not restate it, so this is the domain's round-trip
+    property: the decoder recovers exactly the encoder's quantised latents, for both streams."""
+    import copy
+    config = copy.deepcopy(pcc.OURS_CONFIG)
+    config["entropy_model"] = {"C_bottleneck": 128, "C_hyper_bottleneck": 128}
+    config["entropy_model_map"] = {"C_bottleneck": 2, "C_hyper_bottleneck": 8}
+    model = pcc.ColorModel(config)
+    pcc.codec.init_synthetic(model, 3)
+    model.eval().to(DEV)
+    model.update()
+    assert not hasattr(model.entropy_model, "h_q") and not hasattr(model.entropy_model_map, "h_q")
+    x = pcc.synthetic.shell_frame(20.0, center=[64] * 3, grid=128, seed=3)
+    qc, qf = pcc.synthetic.uniform_q_map(x, 0.5, 0.5)
+    strings, shape, k, coords = model.compress(x.to(DEV), (qc.to(DEV), qf.to(DEV)))
+    assert len(strings) == 2 and len(shape) == 2 and all(len(s) == 2 for s in strings)
+    enc = []
+    for em in (model.entropy_model, model.entropy_model_map):
+        last = em.last
+        enc.append(last["y_symbols"].t().float() + last["params"].F[:, last["params"].F.shape[1] // 2:])
+    out = model.decompress(coordinates=coords, strings=strings, shape=shape, k=k)
+    assert out.shape == (x.shape[0], 6)
+    assert torch.equal(model.last["y_hat"].F, enc[0])
+    assert torch.equal(model.last["Q_hat"].F, enc[1])
+    assert model.last["Q_hat"].F.shape[1] == 2
+    # same call again: deterministic
+    again = model.decompress(coordinates=coords, strings=strings, shape=shape, k=k)
+    assert torch.equal(out, again)
+    res = model(x.to(DEV), (qc.to(DEV), qf.to(DEV)))
+    assert len(res["likelihoods"]["y"]) == 2 and len(res["likelihoods"]["z"]) == 2
+
+
 def test_forward_eval_likelihoods(pcc, oracle):
     """MeanScaleHyperprior_Map.forward (eval): y_hat bit-exact, likelihoods within 1e-5."""
     config = pcc.OURS_CONFIG
