@@ -272,6 +272,10 @@ size_t pcc_conv_wgrad_ws_bytes(int32_t K, int32_t cin, int32_t cout);
 int pcc_conv_wgrad(const pcc_wgrad_args* args, void* stream);
 /* Backward of pcc_gather_rows: out[rows[i]] += g[i] (rows[i] < 0 skipped; NULL = identity). */
 int pcc_scatter_rows_add(const float* g, int32_t c, const int32_t* rows, int64_t n, float* out, void* stream);
+/* Bias gradient of every convolution (grad_bias of ME's ConvolutionBackward): out[j] = sum_i in[i][j] over a
+ * row-major [n x c] matrix, c <= 1024; fixed summation order (deterministic).  ws: pcc_col_sum_ws_bytes(c). */
+size_t pcc_col_sum_ws_bytes(int32_t c);
+int pcc_col_sum(const float* in, int64_t n, int32_t c, float* out, void* ws, size_t ws_bytes, void* stream);
 /* GaussianConditional.forward(training=True) (model/entropy_models.py:330 in train mode): y_noisy =
  * y + U(-0.5, 0.5) is made by the caller; likelihood [n x c] row-major = max(Phi((0.5 - v) / s) -
  * Phi((-0.5 - v) / s), likelihood_bound), v = |y_noisy - mean|, s = max(scale, scale_bound).  The

@@ -50,13 +50,19 @@ class _SparseConv(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             # nbr[k][o] = i  <=>  rnbr[k][i] = o: the same offsets probed from the other side
             rmap = out_map.kernel_map(in_map, ksize, transpose=not transpose)
-            wt = w3.detach().transpose(1, 2).contiguous()
             mode = ctx.mode if (ctx.mode == ops.MODE_EXACT or rmap.n_groups == 1) else ops.MODE_EXACT
-            g_in = ops.conv(g, rmap, wt, None, mode=mode, round_out=False)
+            if mode == ops.MODE_TF32:
+                # the forward pass left the tf32-rounded [K, cout, cin] copy in the cache; its own tensor-core
+                # layout is the rounded weight again (one small kernel, ordered by an event: no host wait)
+                wt = ops.transposed_weight(weight)
+                wtt = ops.transposed_weight(wt)
+            else:
+                wt, wtt = w3.detach().transpose(1, 2).contiguous(), None
+            g_in = ops.conv(g, rmap, wt, None, mode=mode, round_out=False, weight_t=wtt)
         if ctx.needs_input_grad[1]:
             g_w = ops.conv_wgrad(feats, g, kmap, cin, cout, mode=ctx.mode).view(weight.shape)
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            g_b = g.sum(dim=0).view(ctx.bias_shape)
+            g_b = (ops.col_sum(g) if g.shape[1] <= 1024 else g.sum(dim=0)).view(ctx.bias_shape)
         return g_in, g_w, g_b, None, None, None, None
 
 

@@ -247,6 +247,57 @@ static int launch_wgrad_ci(const WgradParams& p, int zt, int ci_idx, int co_idx,
 }
 
 // ---------------------------------------------------------------- scatter-add of rows
+// Column sums of a row-major [n x c] matrix (the bias gradient): block b adds rows b, b + B, ... per column in
+// registers (consecutive threads on consecutive columns, so every row is one coalesced read), its row lanes are
+// combined through shared memory in lane order, and col_sum_final_kernel adds the B partial rows in block order:
+// the same bits on every run.  HBM-bound: 4 * n * c bytes read once.
+constexpr int COLSUM_BLOCKS = 148 * 4;
+
+template <int VEC>
+__global__ void __launch_bounds__(256) col_sum_partial_kernel(const float* __restrict__ in, int64_t n, int c,
+                                                              float* __restrict__ part) {
+  __shared__ float sm[256 * VEC];
+  const int cv = c / VEC;                       // column groups per row (c <= 1024, so cv <= 256 for VEC = 4)
+  const int lanes = cv >= 256 ? 1 : 256 / cv;   // rows a block reads at a time
+  float* dst = part + (int64_t)blockIdx.x * c;
+  for (int col0 = 0; col0 < cv; col0 += 256) {  // more than one pass only for VEC = 1 and c > 256
+    const int lane = threadIdx.x / cv, col = col0 + (cv >= 256 ? threadIdx.x : threadIdx.x % cv);
+    float acc[VEC];
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) acc[v] = 0.f;
+    if (lane < lanes && col < cv) {
+      for (int64_t r = (int64_t)blockIdx.x * lanes + lane; r < n; r += (int64_t)gridDim.x * lanes) {
+        if (VEC == 4) {
+          const float4 x = __ldg(reinterpret_cast<const float4*>(in + r * c) + col);
+          acc[0] += x.x; acc[1 % VEC] += x.y; acc[2 % VEC] += x.z; acc[3 % VEC] += x.w;
+        } else {
+          acc[0] += __ldg(in + r * c + col);
+        }
+      }
+    }
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) sm[threadIdx.x * VEC + v] = acc[v];
+    __syncthreads();
+    if (lane == 0 && col < cv) {
+#pragma unroll
+      for (int v = 0; v < VEC; ++v) {
+        float t = sm[threadIdx.x * VEC + v];
+        for (int l = 1; l < lanes; ++l) t += sm[(threadIdx.x + l * cv) * VEC + v];
+        dst[col * VEC + v] = t;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void col_sum_final_kernel(const float* __restrict__ part, int blocks, int c, float* __restrict__ out) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= c) return;
+  float t = 0.f;
+  for (int b = 0; b < blocks; ++b) t += part[(int64_t)b * c + col];
+  out[col] = t;
+}
+
 __global__ void scatter_rows_add_kernel(const float* __restrict__ g, int c, const int32_t* __restrict__ rows,
                                         int64_t n, float* __restrict__ out) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -377,6 +428,26 @@ int pcc_conv_wgrad(const pcc_wgrad_args* a, void* stream) {
   }
   wgrad_reduce_kernel<<<(unsigned)ceil_div(wn, 256), 256, 0, st>>>(p.part, p.S * splits_nz(sa, sb), wn, a->dweight);
   PCC_CHECK_LAUNCH("wgrad_reduce_kernel");
+  return PCC_OK;
+}
+
+size_t pcc_col_sum_ws_bytes(int32_t c) { return c > 0 ? (size_t)COLSUM_BLOCKS * (size_t)c * sizeof(float) : 0; }
+
+int pcc_col_sum(const float* in, int64_t n, int32_t c, float* out, void* ws, size_t ws_bytes, void* stream) {
+  PCC_REQUIRE(out && c > 0 && c <= 1024 && n >= 0, "bad argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n == 0) {
+    PCC_CHECK_CUDA(cudaMemsetAsync(out, 0, (size_t)c * sizeof(float), st));
+    return PCC_OK;
+  }
+  PCC_REQUIRE(in && ws && ws_bytes >= pcc_col_sum_ws_bytes(c), "workspace too small (pcc_col_sum_ws_bytes)");
+  const bool vec = (c % 4 == 0) && ((reinterpret_cast<uintptr_t>(in) & 15) == 0);
+  const int blocks = (int)std::min<int64_t>(COLSUM_BLOCKS, ceil_div(n, 64));
+  if (vec) col_sum_partial_kernel<4><<<blocks, 256, 0, st>>>(in, n, c, reinterpret_cast<float*>(ws));
+  else col_sum_partial_kernel<1><<<blocks, 256, 0, st>>>(in, n, c, reinterpret_cast<float*>(ws));
+  PCC_CHECK_LAUNCH("col_sum_partial_kernel");
+  col_sum_final_kernel<<<(unsigned)ceil_div(c, 128), 128, 0, st>>>(reinterpret_cast<const float*>(ws), blocks, c, out);
+  PCC_CHECK_LAUNCH("col_sum_final_kernel");
   return PCC_OK;
 }
 

@@ -122,6 +122,38 @@ __device__ __forceinline__ uint32_t sw128(int row, int unit) {
   return (uint32_t)(row * 128 + ((((unit >> 1) ^ (row & 3)) << 5) | ((unit & 1) << 4)));
 }
 
+// index loads that stay where they are written (issued a whole row tile ahead of their first use)
+__device__ __forceinline__ int32_t ld_idx(const int32_t* ptr) {
+  int32_t v;
+  asm volatile("ld.global.nc.s32 %0, [%1];\n" : "=r"(v) : "l"(ptr));
+  return v;
+}
+
+// The row tiles of this CTA (blockIdx.x, + S, ...) that have kernel offset k.  A warp reads the tap masks of
+// its next 32 candidate tiles at once and walks the ballot, so a skipped tile costs no memory latency and an
+// active one 1/32 of one.  Every lane of the warp sees the same sequence.
+struct TileWalk {
+  const uint32_t* tapmask;
+  int64_t tiles, next_base, cur_base;
+  int S, k, lane;
+  uint32_t m;
+  __device__ TileWalk(const uint32_t* tm, int64_t tiles_, int first, int S_, int k_, int lane_)
+      : tapmask(tm), tiles(tiles_), next_base(first), cur_base(first), S(S_), k(k_), lane(lane_), m(0u) {}
+  __device__ __forceinline__ int64_t next() {
+    while (m == 0u) {
+      if (next_base >= tiles) return -1;
+      cur_base = next_base;
+      const int64_t t = cur_base + (int64_t)lane * S;
+      const bool act = t < tiles && (!tapmask || ((__ldg(tapmask + t) >> k) & 1u));
+      m = __ballot_sync(0xffffffffu, act);
+      next_base = cur_base + (int64_t)32 * S;
+    }
+    const int j = __ffs(m) - 1;
+    m &= m - 1u;
+    return cur_base + (int64_t)j * S;
+  }
+};
+
 template <int NT>
 struct Smem {
   static constexpr int STAGES = NT <= 64 ? 4 : 3;
@@ -182,16 +214,24 @@ wgrad_tf32_kernel(const Params p) {
     const char* go_b = reinterpret_cast<const char*>(p.gout) + (int64_t)(u0 * 4) * 4;
     const int64_t in_row = (int64_t)p.cin * 4, go_row = (int64_t)p.cout * 4;
     int it = 0;
-    for (int64_t tile = blockIdx.x; tile < tiles; tile += p.S) {
-      if (p.tapmask && !((p.tapmask[tile] >> k) & 1u)) continue;
-      // this thread's row of each of the tile's four stages
-      int32_t ri[4], ro[4];
+    TileWalk walk(p.tapmask, tiles, (int)blockIdx.x, p.S, k, lane);
+    // this thread's row of each of a tile's four stages; the indices of the NEXT tile are requested before the
+    // copies of the current one are issued, so the index latency is off the tile-to-tile chain
+    int32_t ri[4] = {-1, -1, -1, -1}, ro[4] = {0, 0, 0, 0}, ri_n[4] = {-1, -1, -1, -1}, ro_n[4] = {0, 0, 0, 0};
+    auto request = [&](int64_t tile, int32_t (&a)[4], int32_t (&b)[4]) {
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         const int64_t t = tile * PCC_TILE_M + c * ROWS + r;
-        ri[c] = t < p.n_out ? __ldg(p.nbr + (int64_t)k * p.nbr_stride + t) : -1;
-        ro[c] = ri[c] >= 0 ? (p.order ? __ldg(p.order + t) : (int32_t)t) : -1;
+        const bool in_range = t < p.n_out;
+        a[c] = in_range ? ld_idx(p.nbr + (int64_t)k * p.nbr_stride + t) : -1;
+        b[c] = in_range ? (p.order ? ld_idx(p.order + t) : (int32_t)t) : 0;
       }
+    };
+    int64_t tile = walk.next();
+    if (tile >= 0) request(tile, ri, ro);
+    while (tile >= 0) {
+      const int64_t nxt = walk.next();
+      if (nxt >= 0) request(nxt, ri_n, ro_n);
 #pragma unroll
       for (int c = 0; c < 4; ++c, ++it) {
         const int stage = it % NST;
@@ -205,19 +245,25 @@ wgrad_tf32_kernel(const Params p) {
         for (int s = 0; s < nb; ++s) cp16(b_stage + s * SLAB + off, ok ? src_b + s * 128 : src_b, ok ? 16 : 0);
         cp_arrive_noinc(full_bar(stage));
       }
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        ri[c] = ri_n[c];
+        ro[c] = ro_n[c];
+      }
+      tile = nxt;
     }
     issued = it;
     cp_commit_wait_all();
   } else {
     // ============================ MMA issuer ============================
     int it = 0;
-    if (lane == 0) {
-      constexpr uint32_t idesc = idesc_mn(128, NT);
-      for (int64_t tile = blockIdx.x; tile < tiles; tile += p.S) {
-        if (p.tapmask && !((p.tapmask[tile] >> k) & 1u)) continue;
-        for (int c = 0; c < 4; ++c, ++it) {
-          const int stage = it % NST;
-          mbar_wait(full_bar(stage), (uint32_t)((it / NST) & 1));
+    constexpr uint32_t idesc = idesc_mn(128, NT);
+    TileWalk walk(p.tapmask, tiles, (int)blockIdx.x, p.S, k, lane);
+    for (int64_t tile = walk.next(); tile >= 0; tile = walk.next()) {
+      if (lane == 0) {
+        for (int c = 0; c < 4; ++c) {
+          const int stage = (it + c) % NST;
+          mbar_wait(full_bar(stage), (uint32_t)(((it + c) / NST) & 1));
           fence_proxy_async();
           tc_fence_after();
           const uint32_t a_stage = base + stage * S::STAGE_BYTES;
@@ -225,12 +271,14 @@ wgrad_tf32_kernel(const Params p) {
 #pragma unroll
           for (int kk = 0; kk < ROWS / 8; ++kk)
             umma_tf32(tmem_acc, mn_desc(a_stage + kk * 1024), mn_desc(b_stage + kk * 1024), idesc,
-                      (it > 0 || kk > 0) ? 1u : 0u);
+                      (it + c > 0 || kk > 0) ? 1u : 0u);
           umma_commit(empty_bar(stage));
         }
       }
-      if (it > 0) umma_commit(accum_bar);
+      it += 4;
+      __syncwarp();
     }
+    if (lane == 0 && it > 0) umma_commit(accum_bar);
     __syncwarp();
   }
 

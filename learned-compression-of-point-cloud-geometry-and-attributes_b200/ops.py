@@ -391,17 +391,27 @@ def transposed_weight(weight):
     ver = (weight._version, tuple(weight.shape), str(weight.device), weight.data_ptr())
     hit = _wt_cache.get(key)
     if hit is not None and hit[0]() is weight and hit[1] == ver:
-        return hit[2]
+        return _wt_acquire(hit)
     with cache_lock:
-        return _transposed_weight_build(weight, key, ver)
+        return _wt_acquire(_transposed_weight_build(weight, key, ver))
+
+
+def _wt_acquire(hit):
+    """The copy was produced on hit[4]; any other stream orders itself behind the producing kernel with an
+    event wait (no host synchronisation: in training every weight is re-laid-out every step)."""
+    cur = torch.cuda.current_stream()
+    if cur.cuda_stream != hit[4]:
+        cur.wait_event(hit[3])
+        hit[2].record_stream(cur)
+    return hit[2]
 
 
 def _transposed_weight_build(weight, key, ver):
     import weakref
     hit = _wt_cache.get(key)
     if hit is not None and hit[0]() is weight and hit[1] == ver:
-        return hit[2]
-    if len(_wt_cache) > 512:
+        return hit
+    if len(_wt_cache) > 256:
         for k in [k for k, v in _wt_cache.items() if v[0]() is None]:
             del _wt_cache[k]
     w = weight.detach()
@@ -410,20 +420,24 @@ def _transposed_weight_build(weight, key, ver):
     wt = torch.empty((K, cout, cin), dtype=torch.float32, device=w.device)
     check(_L().pcc_weight_transpose(_ptr(w), K, cin, cout, _ptr(wt), _stream()), "pcc_weight_transpose")
     _count()
-    publish(wt)
-    _wt_cache[key] = (weakref.ref(weight), ver, wt)
-    return wt
+    ev = torch.cuda.Event()
+    ev.record()
+    hit = (weakref.ref(weight), ver, wt, ev, torch.cuda.current_stream().cuda_stream)
+    _wt_cache[key] = hit
+    return hit
 
 
 CONV_ROUND_OUT_TF32 = 1
 
 
 def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None, residual=None,
-         res_rows=None, out=None, mode=None, round_out=None):
+         res_rows=None, out=None, mode=None, round_out=None, weight_t=None):
     """out[o] = epilogue(sum_k feats[nbr[k,o]] @ weight[k]).
 
     weight: [K, cin, cout] (or [cin, cout] for K == 1), bias: [1, cout] or [cout].
     film: [n_film, 2*cf] (beta | gamma), cf in {cout, 1}; residual: [n_res, cout].
+    weight_t: the [K, cout, cin] layout of `weight` when the caller already holds it (the data gradient does:
+    it is the forward weight); otherwise the tensor-core path takes it from the cache of transposed_weight.
     """
     _need_cuda(feats, "feats")
     feats = feats.contiguous()
@@ -446,7 +460,14 @@ def conv(feats, kmap, weight, bias=None, act=ACT_NONE, film=None, film_rows=None
     a.n_in = feats.shape[0]
     a.cin, a.cout = cin, cout
     a.weight = w.data_ptr()
-    wt = transposed_weight(weight) if mode == MODE_TF32 else None
+    if mode != MODE_TF32:
+        wt = None
+    elif weight_t is not None:
+        wt = weight_t.contiguous()
+        if tuple(wt.shape[-3:] if wt.dim() == 3 else (1,) + tuple(wt.shape)) != (K, cout, cin):
+            raise _lib.PccError(f"weight_t {tuple(wt.shape)} is not the [K, cout, cin] layout of {tuple(w.shape)}")
+    else:
+        wt = transposed_weight(weight)
     a.weight_t = None if wt is None else wt.data_ptr()
     b = None if bias is None else bias.contiguous()
     a.bias = None if b is None else b.data_ptr()
@@ -567,6 +588,19 @@ def conv_wgrad(feats, gout, kmap, cin, cout, mode=MODE_EXACT):
         check(_L().pcc_conv_wgrad(ctypes.byref(a), _stream()), "pcc_conv_wgrad")
     _count(kmap.n_groups + 1)
     return dw
+
+
+def col_sum(x):
+    """[n, c] -> [c] column sums in a fixed order (the bias gradient; pcc_col_sum)."""
+    _need_cuda(x, "x")
+    x = x.contiguous()
+    n, c = x.shape
+    out = torch.empty((c,), dtype=torch.float32, device=x.device)
+    wsb = _L().pcc_col_sum_ws_bytes(c)
+    ws = _ws(wsb, x.device)
+    check(_L().pcc_col_sum(_ptr(x), n, c, _ptr(out), _ptr(ws), wsb, _stream()), "pcc_col_sum")
+    _count(2 if n else 0)
+    return out
 
 
 def scatter_rows_add(g, rows, n_dst):

@@ -393,3 +393,16 @@ def test_tensor_core_weight_gradient(pcc, oracle, cin, cout, ks, stride, transpo
         pcc.ops.set_tap_groups(None)
     assert torch.equal(got, again)
     _close(got.cpu().numpy(), ref.cpu().numpy(), 2e-3, "tensor-core weight gradient")
+
+
+@pytest.mark.parametrize("n,c", [(0, 8), (1, 3), (1000, 2), (4097, 64), (70001, 128), (333, 256), (5000, 7), (900, 1024),
+                                 (3000, 300)])
+def test_column_sum_is_the_bias_gradient(pcc, n, c):
+    """pcc_col_sum against a float64 sum (1e-6 relative to the column's absolute sum), twice the same bits."""
+    x = torch.randn((n, c), generator=torch.Generator().manual_seed(n + c)).to(DEV)
+    got = pcc.ops.col_sum(x)
+    again = pcc.ops.col_sum(x)
+    assert got.shape == (c,) and torch.equal(got, again)
+    ref = x.double().sum(0)
+    scale = x.double().abs().sum(0).clamp_min(1e-30)
+    assert float(((got.double() - ref).abs() / scale).max()) <= 1e-6 if n else float(got.abs().max()) == 0.0

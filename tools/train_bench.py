@@ -35,10 +35,12 @@ def main():
     ap.add_argument("--batch", type=int, default=8)
     ap.add_argument("--radius", type=float, default=56.0)
     ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--layers", default=None)
     ap.add_argument("--mode", default="exact", choices=["exact", "tf32"],
                     help="tf32: forward and data gradient of the >= 32-channel layers on tcgen05 (weight gradient fp32)")
+    ap.add_argument("--host-profile", default=None, help="write a cProfile table (with callers) of one step here")
+    ap.add_argument("--torch-profile", default=None, help="write a torch.profiler table of one step here")
     a = ap.parse_args()
     import pcc_b200 as pcc
     dev = "cuda:0"
@@ -103,6 +105,29 @@ def main():
     fwd = sum(m[0].elapsed_time(m[1]) for m in per) / a.steps
     bwd = sum(m[1].elapsed_time(m[2]) for m in per) / a.steps
     opt_ms = sum(m[2].elapsed_time(m[3]) for m in per) / a.steps
+    step_ms = [round(m[0].elapsed_time(m[3]), 1) for m in per]
+    if a.host_profile:
+        import cProfile, pstats, io
+        pr = cProfile.Profile()
+        pr.enable()
+        step()
+        torch.cuda.synchronize()
+        pr.disable()
+        buf = io.StringIO()
+        st = pstats.Stats(pr, stream=buf).sort_stats("tottime")
+        st.print_stats(40)
+        st.print_callers("tolist|item|nonzero|synchronize|_local_scalar|masked_select|index|unique")
+        with open(a.host_profile, "w") as f:
+            f.write(buf.getvalue())
+    if a.torch_profile:
+        from torch.profiler import profile, ProfilerActivity
+        with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+            step()
+            torch.cuda.synchronize()
+        with open(a.torch_profile, "w") as f:
+            f.write(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=70))
+            f.write("\n\n")
+            f.write(prof.key_averages().table(sort_by="self_cpu_time_total", row_limit=30, max_name_column_width=70))
     # one profiled step: per-launch CUDA events around every convolution / weight-gradient launch
     pcc.ops.start_conv_profile()
     step()
@@ -132,6 +157,7 @@ def main():
     print(json.dumps({
         "metric": "training step points/sec (forward + loss + backward + Adam)", "value": n / (total_ms / 1e3),
         "unit": "points/s", "ms_per_step": total_ms, "points_per_batch": n, "batch": a.batch,
+        "step_ms": step_ms, "reserved_gb": round(torch.cuda.memory_reserved() / 2**30, 2),
         "phases_ms": {"forward+loss": fwd, "backward": bwd, "clip+adam+aux": opt_ms},
         "gpu_launches_per_step": launches / a.steps, "last_loss": loss, "dtype": "f32" if a.mode == "exact" else "tf32",
         "tensor_core_conv": None if not tc else {
