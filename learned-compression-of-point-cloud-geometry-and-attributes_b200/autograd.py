@@ -48,16 +48,22 @@ class _SparseConv(torch.autograd.Function):
         K, cin, cout = w3.shape
         g_in = g_w = g_b = None
         if ctx.needs_input_grad[0]:
-            # nbr[k][o] = i  <=>  rnbr[k][i] = o: the same offsets probed from the other side
-            rmap = out_map.kernel_map(in_map, ksize, transpose=not transpose)
+            # nbr[k][o] = i  <=>  rnbr[k][i] = o: the same offsets probed from the other side.  On ONE map with an
+            # odd kernel the other side is the mirrored offset of the same kernel map (c_o = c_i - d_k = c_i +
+            # d_{K-1-k}), so the data gradient runs over the forward map with the weights flipped along K and no
+            # second map is built
+            mirrored = in_map is out_map and ksize % 2 == 1 and not transpose
+            rmap = kmap if mirrored else out_map.kernel_map(in_map, ksize, transpose=not transpose)
             mode = ctx.mode if (ctx.mode == ops.MODE_EXACT or rmap.n_groups == 1) else ops.MODE_EXACT
             if mode == ops.MODE_TF32:
                 # the forward pass left the tf32-rounded [K, cout, cin] copy in the cache; its own tensor-core
                 # layout is the rounded weight again (one small kernel, ordered by an event: no host wait)
                 wt = ops.transposed_weight(weight)
+                wt = wt.flip(0) if mirrored else wt
                 wtt = ops.transposed_weight(wt)
             else:
-                wt, wtt = w3.detach().transpose(1, 2).contiguous(), None
+                wt, wtt = w3.detach().transpose(1, 2), None
+                wt = (wt.flip(0) if mirrored else wt).contiguous()
             g_in = ops.conv(g, rmap, wt, None, mode=mode, round_out=False, weight_t=wtt)
         if ctx.needs_input_grad[1]:
             g_w = ops.conv_wgrad(feats, g, kmap, cin, cout, mode=ctx.mode).view(weight.shape)

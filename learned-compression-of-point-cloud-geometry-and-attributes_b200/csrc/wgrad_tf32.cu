@@ -9,6 +9,8 @@
 //     with cp.async.mbarrier.arrive.noinc (no thread waits for its copies);
 //   * one elected lane issues 4 x tcgen05.mma (M = 128, N = cout tile, K = 8 rows) per stage; the fp32
 //     accumulator [128 ci x cout] stays in TMEM across ALL row tiles of the CTA;
+//   * layers with cin = 64 / 32 put 2 / 4 kernel offsets side by side in the M = 128 rows (each offset gathers its
+//     own `in` rows into its slabs; the gout rows are shared), so narrow layers use the whole MMA and gather B once;
 //   * the kernel map's tap masks skip row tiles without offset k; the row range is cut into S splits
 //     whose partial tiles are added in a fixed order by wgrad_reduce (deterministic).
 // MN-major operands of a 32-bit type have ONE legal shared-memory layout, SWIZZLE_128B_BASE32B (descriptor
@@ -38,7 +40,7 @@ struct Params {
   const int32_t* order;
   float* part;  // [S][K][cin][cout]
   int64_t nbr_stride, n_out;
-  int cin, cout, K, k_lo, S;
+  int cin, cout, K, k_lo, k_hi, S;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -129,22 +131,22 @@ __device__ __forceinline__ int32_t ld_idx(const int32_t* ptr) {
   return v;
 }
 
-// The row tiles of this CTA (blockIdx.x, + S, ...) that have kernel offset k.  A warp reads the tap masks of
+// The row tiles of this CTA (blockIdx.x, + S, ...) that have one of the CTA's kernel offsets (kmask).  A warp reads the tap masks of
 // its next 32 candidate tiles at once and walks the ballot, so a skipped tile costs no memory latency and an
 // active one 1/32 of one.  Every lane of the warp sees the same sequence.
 struct TileWalk {
   const uint32_t* tapmask;
   int64_t tiles, next_base, cur_base;
-  int S, k, lane;
-  uint32_t m;
-  __device__ TileWalk(const uint32_t* tm, int64_t tiles_, int first, int S_, int k_, int lane_)
-      : tapmask(tm), tiles(tiles_), next_base(first), cur_base(first), S(S_), k(k_), lane(lane_), m(0u) {}
+  int S, lane;
+  uint32_t kmask, m;
+  __device__ TileWalk(const uint32_t* tm, int64_t tiles_, int first, int S_, uint32_t kmask_, int lane_)
+      : tapmask(tm), tiles(tiles_), next_base(first), cur_base(first), S(S_), lane(lane_), kmask(kmask_), m(0u) {}
   __device__ __forceinline__ int64_t next() {
     while (m == 0u) {
       if (next_base >= tiles) return -1;
       cur_base = next_base;
       const int64_t t = cur_base + (int64_t)lane * S;
-      const bool act = t < tiles && (!tapmask || ((__ldg(tapmask + t) >> k) & 1u));
+      const bool act = t < tiles && (!tapmask || (__ldg(tapmask + t) & kmask) != 0u);
       m = __ballot_sync(0xffffffffu, act);
       next_base = cur_base + (int64_t)32 * S;
     }
@@ -164,8 +166,11 @@ struct Smem {
   static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;  // barriers + alignment slack
 };
 
-// grid (S, offsets of this launch, ci tiles); NT = cout rounded up to 64 / 128 / 256
-template <int NT>
+// grid (S, offsets of this launch / NS, ci tiles); NT = cout rounded up to 64 / 128 / 256.
+// NS > 1 (cin = 128 / NS): the M = 128 rows of the MMA hold NS kernel offsets side by side — offset k0 + j owns
+// A slabs [j * cin / 32, (j + 1) * cin / 32) and accumulator lanes [j * cin, (j + 1) * cin) — so a narrow layer
+// fills the tensor core's M dimension, and the gathered gout rows (B) are shared by the NS offsets.
+template <int NT, int NS>
 __global__ void __launch_bounds__(THREADS, NT <= 128 ? 2 : 1)
 wgrad_tf32_kernel(const Params p) {
   extern __shared__ unsigned char smem_raw[];
@@ -181,9 +186,11 @@ wgrad_tf32_kernel(const Params p) {
   const uint32_t tmem_slot = bar_base + 8u * (2 * NST + 1);
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(sbase + S::BAR_OFFSET + 8 * (2 * NST + 1));
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int k = p.k_lo + blockIdx.y;
-  const int ci0 = blockIdx.z * 128;
-  const int na = min(4, (p.cin - ci0) / 32);  // live 32-channel slabs of A
+  const int k0 = p.k_lo + blockIdx.y * NS;               // first kernel offset of this CTA
+  const int nk = min(NS, p.k_hi - k0);                    // live offsets
+  const uint32_t kmask = ((1u << nk) - 1u) << k0;
+  const int ci0 = NS > 1 ? 0 : blockIdx.z * 128;
+  const int spo = NS > 1 ? p.cin / 32 : min(4, (p.cin - ci0) / 32);  // live 32-channel slabs of A per offset
   const int nb = p.cout / 32;                 // live slabs of B
   const int64_t tiles = (p.n_out + PCC_TILE_M - 1) / PCC_TILE_M;
 
@@ -214,16 +221,24 @@ wgrad_tf32_kernel(const Params p) {
     const char* go_b = reinterpret_cast<const char*>(p.gout) + (int64_t)(u0 * 4) * 4;
     const int64_t in_row = (int64_t)p.cin * 4, go_row = (int64_t)p.cout * 4;
     int it = 0;
-    TileWalk walk(p.tapmask, tiles, (int)blockIdx.x, p.S, k, lane);
+    TileWalk walk(p.tapmask, tiles, (int)blockIdx.x, p.S, kmask, lane);
     // this thread's row of each of a tile's four stages; the indices of the NEXT tile are requested before the
     // copies of the current one are issued, so the index latency is off the tile-to-tile chain
-    int32_t ri[4] = {-1, -1, -1, -1}, ro[4] = {0, 0, 0, 0}, ri_n[4] = {-1, -1, -1, -1}, ro_n[4] = {0, 0, 0, 0};
-    auto request = [&](int64_t tile, int32_t (&a)[4], int32_t (&b)[4]) {
+    int32_t ri[4][NS], ro[4], ri_n[4][NS], ro_n[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      ro[c] = ro_n[c] = 0;
+#pragma unroll
+      for (int j = 0; j < NS; ++j) ri[c][j] = ri_n[c][j] = -1;
+    }
+    auto request = [&](int64_t tile, int32_t (&a)[4][NS], int32_t (&b)[4]) {
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         const int64_t t = tile * PCC_TILE_M + c * ROWS + r;
         const bool in_range = t < p.n_out;
-        a[c] = in_range ? ld_idx(p.nbr + (int64_t)k * p.nbr_stride + t) : -1;
+#pragma unroll
+        for (int j = 0; j < NS; ++j)
+          a[c][j] = (in_range && j < nk) ? ld_idx(p.nbr + (int64_t)(k0 + j) * p.nbr_stride + t) : -1;
         b[c] = in_range ? (p.order ? ld_idx(p.order + t) : (int32_t)t) : 0;
       }
     };
@@ -238,17 +253,24 @@ wgrad_tf32_kernel(const Params p) {
         if (it >= NST) mbar_wait(empty_bar(stage), (uint32_t)(((it / NST) - 1) & 1));
         const uint32_t a_stage = base + stage * S::STAGE_BYTES;
         const uint32_t b_stage = a_stage + S::A_BYTES;
-        const bool ok = ri[c] >= 0;
-        const char* src_a = ok ? in_b + ri[c] * in_row : reinterpret_cast<const char*>(p.in);
-        const char* src_b = ok ? go_b + ro[c] * go_row : reinterpret_cast<const char*>(p.gout);
-        for (int s = 0; s < na; ++s) cp16(a_stage + s * SLAB + off, ok ? src_a + s * 128 : src_a, ok ? 16 : 0);
-        for (int s = 0; s < nb; ++s) cp16(b_stage + s * SLAB + off, ok ? src_b + s * 128 : src_b, ok ? 16 : 0);
+        bool any = false;
+#pragma unroll
+        for (int j = 0; j < NS; ++j) {
+          const bool ok = ri[c][j] >= 0;
+          any |= ok;
+          const char* src_a = ok ? in_b + ri[c][j] * in_row : reinterpret_cast<const char*>(p.in);
+          for (int s = 0; s < spo; ++s)
+            cp16(a_stage + (j * spo + s) * SLAB + off, ok ? src_a + s * 128 : src_a, ok ? 16 : 0);
+        }
+        const char* src_b = any ? go_b + ro[c] * go_row : reinterpret_cast<const char*>(p.gout);
+        for (int s = 0; s < nb; ++s) cp16(b_stage + s * SLAB + off, any ? src_b + s * 128 : src_b, any ? 16 : 0);
         cp_arrive_noinc(full_bar(stage));
       }
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
-        ri[c] = ri_n[c];
         ro[c] = ro_n[c];
+#pragma unroll
+        for (int j = 0; j < NS; ++j) ri[c][j] = ri_n[c][j];
       }
       tile = nxt;
     }
@@ -258,7 +280,7 @@ wgrad_tf32_kernel(const Params p) {
     // ============================ MMA issuer ============================
     int it = 0;
     constexpr uint32_t idesc = idesc_mn(128, NT);
-    TileWalk walk(p.tapmask, tiles, (int)blockIdx.x, p.S, k, lane);
+    TileWalk walk(p.tapmask, tiles, (int)blockIdx.x, p.S, kmask, lane);
     for (int64_t tile = walk.next(); tile >= 0; tile = walk.next()) {
       if (lane == 0) {
         for (int c = 0; c < 4; ++c) {
@@ -289,8 +311,11 @@ wgrad_tf32_kernel(const Params p) {
       tc_fence_after();
     }
     const int quad = warp & 3;
-    const int ci = ci0 + quad * 32 + lane;
-    float* dst = p.part + (((int64_t)blockIdx.x * p.K + k) * p.cin + ci) * p.cout;
+    const int row = quad * 32 + lane;                       // accumulator lane
+    const int j = NS > 1 ? row / p.cin : 0;                 // which of the CTA's offsets it belongs to
+    const int ci = NS > 1 ? row - j * p.cin : ci0 + row;
+    const bool row_live = NS > 1 ? j < nk : ci < p.cin;
+    float* dst = p.part + (((int64_t)blockIdx.x * p.K + (k0 + (row_live ? j : 0))) * p.cin + (row_live ? ci : 0)) * p.cout;
     constexpr int HALF = NT / 2 >= 32 ? NT / 2 : 32;
     for (int c0 = (warp >> 2) * HALF; c0 < ((warp >> 2) + 1) * HALF && c0 < p.cout; c0 += 32) {
       uint32_t v[32];
@@ -300,7 +325,7 @@ wgrad_tf32_kernel(const Params p) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = 0u;
       }
-      if (ci < p.cin) {
+      if (row_live) {
 #pragma unroll
         for (int i = 0; i < 32; i += 4)
           *reinterpret_cast<float4*>(dst + c0 + i) = make_float4(__uint_as_float(v[i]), __uint_as_float(v[i + 1]),
@@ -313,17 +338,25 @@ wgrad_tf32_kernel(const Params p) {
   if (warp == PWARPS) tmem_dealloc(tmem_acc, NT);
 }
 
-template <int NT>
+template <int NT, int NS>
 static int launch(const Params& p, int k_count, int ci_tiles, cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
-    PCC_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tf32_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<NT>::TOTAL));
+    PCC_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tf32_kernel<NT, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        Smem<NT>::TOTAL));
     attr_done = true;
   }
-  dim3 grid((unsigned)p.S, (unsigned)k_count, (unsigned)ci_tiles);
-  wgrad_tf32_kernel<NT><<<grid, THREADS, Smem<NT>::TOTAL, st>>>(p);
+  dim3 grid((unsigned)p.S, (unsigned)ceil_div(k_count, NS), (unsigned)ci_tiles);
+  wgrad_tf32_kernel<NT, NS><<<grid, THREADS, Smem<NT>::TOTAL, st>>>(p);
   PCC_CHECK_LAUNCH("wgrad_tf32_kernel");
   return PCC_OK;
+}
+
+template <int NT>
+static int launch_ns(const Params& p, int ns, int k_count, int ci_tiles, cudaStream_t st) {
+  if (ns == 4) return launch<NT, 4>(p, k_count, ci_tiles, st);
+  if (ns == 2) return launch<NT, 2>(p, k_count, ci_tiles, st);
+  return launch<NT, 1>(p, k_count, ci_tiles, st);
 }
 
 }  // namespace wgtc
@@ -345,8 +378,10 @@ int wgrad_tf32(const pcc_wgrad_args* a, int* splits, cudaStream_t st) {
   const int per = (a->K + ng - 1) / ng;
   const int64_t tiles = ceil_div(a->n_out, PCC_TILE_M);
   const int ci_tiles = (int)ceil_div(a->cin, 128);
-  // two CTAs per SM over (splits x offsets of a launch x ci tiles); never more splits than row tiles, at most 64
-  int64_t s = (int64_t)2 * sm_count() / std::max(1, per * ci_tiles);
+  // narrow layers put 128 / cin kernel offsets side by side in the MMA's M dimension
+  const int ns = a->cin == 32 ? 4 : a->cin == 64 ? 2 : 1;
+  // two CTAs per SM over (splits x offset stacks of a launch x ci tiles); never more splits than row tiles, at most 64
+  int64_t s = (int64_t)2 * sm_count() / std::max(1, (int)ceil_div(per, ns) * ci_tiles);
   s = std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(s, tiles), 64));
   p.S = (int)s;
   *splits = p.S;
@@ -354,12 +389,13 @@ int wgrad_tf32(const pcc_wgrad_args* a, int* splits, cudaStream_t st) {
     p.k_lo = g * per;
     const int k_hi = std::min((g + 1) * per, (int)a->K);
     if (p.k_lo >= k_hi) break;
+    p.k_hi = k_hi;
     p.order = a->order ? a->order + (int64_t)g * a->n_out : nullptr;
     p.tapmask = a->tapmask ? a->tapmask + (int64_t)g * tiles : nullptr;
     int rc;
-    if (a->cout <= 64) rc = launch<64>(p, k_hi - p.k_lo, ci_tiles, st);
-    else if (a->cout <= 128) rc = launch<128>(p, k_hi - p.k_lo, ci_tiles, st);
-    else rc = launch<256>(p, k_hi - p.k_lo, ci_tiles, st);
+    if (a->cout <= 64) rc = launch_ns<64>(p, ns, k_hi - p.k_lo, ci_tiles, st);
+    else if (a->cout <= 128) rc = launch_ns<128>(p, ns, k_hi - p.k_lo, ci_tiles, st);
+    else rc = launch_ns<256>(p, ns, k_hi - p.k_lo, ci_tiles, st);
     if (rc != PCC_OK) return rc;
   }
   return PCC_OK;

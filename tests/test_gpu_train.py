@@ -375,7 +375,8 @@ def test_training_step_in_tensor_core_mode(pcc):
 
 @pytest.mark.parametrize("cin,cout,ks,stride,transpose,groups", [
     (128, 128, 3, 1, False, 1), (64, 64, 3, 1, False, 3), (128, 256, 3, 1, False, None), (192, 256, 3, 1, False, None),
-    (64, 32, 3, 1, False, None), (128, 192, 2, 2, True, None), (64, 128, 3, 2, False, None), (32, 32, 1, 1, False, None)])
+    (64, 32, 3, 1, False, None), (128, 192, 2, 2, True, None), (64, 128, 3, 2, False, None), (32, 32, 1, 1, False, None),
+    (32, 64, 3, 1, False, 1), (64, 64, 3, 1, False, 1), (32, 96, 2, 2, True, None), (96, 64, 3, 1, False, None)])
 def test_tensor_core_weight_gradient(pcc, oracle, cin, cout, ks, stride, transpose, groups):
     """wgrad_tf32_kernel (tcgen05, MN-major gathered operands) against the fp32 weight gradient: operands are
     truncated to tf32 (10-bit mantissa), accumulation is fp32: within 2e-3 of the largest entry; deterministic."""
