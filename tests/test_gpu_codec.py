@@ -67,6 +67,38 @@ def test_decompress_accepts_float_unsorted_coordinates(pcc, oracle):
     assert torch.equal(a, b)
 
 
+@pytest.mark.parametrize("case", ["one_voxel", "two_far_voxels", "short_line", "grid_corner", "tiny_cube"])
+def test_degenerate_clouds_bit_exact(pcc, oracle, case):
+    """Clouds far below one 128-row tile, isolated voxels, voxels at the origin corner of the grid: same
+    strings, point counts and decoded cloud as the oracle (every map, top-k and coder call sees n < 128,
+    k = 1 or a single symbol row)."""
+    pts = {
+        "one_voxel": [[40, 41, 42]],
+        "two_far_voxels": [[3, 5, 7], [100, 90, 80]],
+        "short_line": [[10 + i, 20, 30] for i in range(5)],
+        "grid_corner": [[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1], [127, 127, 127]],
+        "tiny_cube": [[60 + a, 60 + b, 60 + c] for a in range(3) for b in range(3) for c in range(3)],
+    }[case]
+    g = torch.Generator().manual_seed(len(pts))
+    x = torch.cat([torch.tensor(pts, dtype=torch.float32), torch.rand((len(pts), 3), generator=g)], 1)
+    model = pcc.ColorModel(pcc.OURS_CONFIG)
+    pcc.codec.init_synthetic(model, 4)
+    model.eval()
+    params = pcc.codec.export_params(model)
+    model.to(DEV)
+    model.update()
+    qc, qf = pcc.synthetic.uniform_q_map(x, 0.25, 0.75)
+    oc = oracle.OracleCodec(params, pcc.OURS_CONFIG)
+    o_strings, o_shape, o_k, o_coords = oc.compress(x.numpy(), qc.numpy(), qf.numpy())
+    strings, shape, k, coords = model.compress(x.to(DEV), (qc.to(DEV), qf.to(DEV)))
+    assert strings == o_strings and shape == o_shape and k == o_k
+    assert np.array_equal(coords.cpu().numpy(), o_coords)
+    out = model.decompress(coordinates=coords, strings=strings, shape=shape, k=k)
+    o_out = oc.decompress(o_coords, o_strings, o_shape, o_k)
+    assert out.shape == (len(pts), 6)
+    assert np.array_equal(out.cpu().numpy(), o_out)
+
+
 def test_prune_before_refine_variant_bit_exact(pcc, oracle):
     """g_s.dense = False (model/transforms.py:160-163, model/blocks.py:156-175): occupancy is predicted and
     pruned before conv_2.  No shipped config sets it; the switch is on the path."""
