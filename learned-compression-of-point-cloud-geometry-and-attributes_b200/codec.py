@@ -603,6 +603,9 @@ class ColorModel(CompressionModel):
         dev = self.device
         x = x.to(dev, non_blocking=True)
         N = x.shape[0]
+        if N == 0 or x.dim() != 2 or x.shape[1] < 6:
+            # the reference hands this to ME.SparseTensor / torch.cat, which reject it with a shape error
+            raise PccError(f"compress needs a non-empty [N, 6] cloud (xyz, rgb); got {tuple(x.shape)}")
         pts = torch.cat([torch.zeros((N, 1), device=dev), x[:, :3]], dim=1).int()
         feats = torch.cat([torch.ones((N, 1), device=dev), x[:, 3:6]], dim=1)
         inp = _canonical(pts, feats, 1)
@@ -712,6 +715,9 @@ class ColorModel(CompressionModel):
                                                  dtype=coordinates.dtype), coordinates], dim=1)
         if coordinates.is_floating_point():
             coordinates = torch.floor(coordinates)
+        if coordinates.shape[0] == 0 or len(k) != 3 or any(len(ki) == 0 for ki in k):
+            raise PccError("decompress needs the latent coordinates and the three per-batch point counts of a "
+                           f"non-empty cloud; got {tuple(coordinates.shape)} coordinates, k = {k}")
         with stage("dec.maps"):
             y_map, _ = ops.canonical_map(coordinates.int(), 8)
             z_map = y_map.stride2().stride2()  # g_s.down_conv twice, only .C is used (:188-191)
