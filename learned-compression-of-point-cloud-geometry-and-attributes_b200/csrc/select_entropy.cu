@@ -128,26 +128,62 @@ topk_hist_kernel(const float* __restrict__ logits, int64_t stride, int64_t m, in
     if (sh[i]) atomicAdd(&hist[i], sh[i]);
 }
 
-__global__ void topk_find_kernel(int pass, TopkState* __restrict__ state, uint32_t* __restrict__ hist) {
-  // single thread: walk bins from the top until the cumulative count covers `remaining`
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+// One block: the first bin from the top whose cumulative count covers `remaining` becomes the next digit of the
+// threshold key.  Thread t owns bins/256 consecutive bins (descending), a block scan gives the count above them;
+// exactly one bin satisfies  count_above < remaining <= count_above + h  (the top bin when remaining == 0).
+constexpr int TF_THREADS = 256;
+__global__ void __launch_bounds__(TF_THREADS)
+topk_find_kernel(int pass, TopkState* __restrict__ state, uint32_t* __restrict__ hist) {
+  __shared__ long long part[TF_THREADS];
+  __shared__ int s_sel;
+  __shared__ long long s_cum;
+  const int t = threadIdx.x;
   const int bins = pass_bins(pass);
-  int64_t rem = state->remaining;
-  int64_t cum = 0;
-  int sel = 0;
-  for (int b = bins - 1; b >= 0; --b) {
-    const uint32_t h = hist[b];
-    if (cum + h >= rem) {
-      sel = b;
-      break;
-    }
-    cum += h;
+  const int per = bins / TF_THREADS;  // 8 or 4
+  const long long rem = state->remaining;
+  uint32_t h[TK_BINS / TF_THREADS];
+  long long tsum = 0;
+#pragma unroll
+  for (int j = 0; j < TK_BINS / TF_THREADS; ++j) {
+    h[j] = j < per ? hist[bins - 1 - (t * per + j)] : 0u;
+    tsum += h[j];
   }
-  state->remaining = rem - cum;
-  const int shift = pass_shift(pass);
-  state->prefix |= (uint32_t)sel << shift;
-  state->prefix_mask |= ((uint32_t)bins - 1) << shift;
-  for (int b = 0; b < TK_BINS; ++b) hist[b] = 0;
+  part[t] = tsum;
+  if (t == 0) s_sel = -1;
+  __syncthreads();
+  for (int off = 1; off < TF_THREADS; off <<= 1) {  // inclusive scan of the per-thread counts
+    const long long v = t >= off ? part[t - off] : 0;
+    __syncthreads();
+    part[t] += v;
+    __syncthreads();
+  }
+  long long cum = part[t] - tsum;  // count in the bins above this thread's
+#pragma unroll
+  for (int j = 0; j < TK_BINS / TF_THREADS; ++j) {
+    if (j < per) {
+      const int d = t * per + j;
+      const long long incl = cum + h[j];
+      if (incl >= rem && (d == 0 || cum < rem)) {
+        s_sel = bins - 1 - d;
+        s_cum = cum;
+      }
+      cum = incl;
+    }
+  }
+  __syncthreads();
+  if (t == 0) {
+    int sel = s_sel;
+    long long above = s_cum;
+    if (sel < 0) {  // fewer keys than `remaining` (k <= m rules it out): bottom bin, everything counted
+      sel = 0;
+      above = part[TF_THREADS - 1];
+    }
+    state->remaining = rem - above;
+    const int shift = pass_shift(pass);
+    state->prefix |= (uint32_t)sel << shift;
+    state->prefix_mask |= ((uint32_t)bins - 1) << shift;
+  }
+  for (int b = t; b < TK_BINS; b += TF_THREADS) hist[b] = 0;
 }
 
 __global__ void topk_eq_flags_kernel(const float* __restrict__ logits, int64_t stride, int64_t m,
@@ -498,7 +534,7 @@ int pcc_topk_select(const float* logits, int64_t stride, int64_t m, int64_t k, i
   for (int pass = 0; pass < 3; ++pass) {
     topk_hist_kernel<<<hgrid, THREADS, 0, st>>>(logits, stride, m, pass, state, hist);
     PCC_CHECK_LAUNCH("topk_hist_kernel");
-    topk_find_kernel<<<1, 32, 0, st>>>(pass, state, hist);
+    topk_find_kernel<<<1, TF_THREADS, 0, st>>>(pass, state, hist);
     PCC_CHECK_LAUNCH("topk_find_kernel");
   }
   topk_eq_flags_kernel<<<grid_for(m), THREADS, 0, st>>>(logits, stride, m, state, eq);
