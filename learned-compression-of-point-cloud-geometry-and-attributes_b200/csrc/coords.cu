@@ -236,19 +236,23 @@ kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict_
   const int64_t j = (int64_t)blockIdx.x * PCC_TILE_M + threadIdx.x;  // tile row
   const bool live = j < n_out;
   int b = 0, x = 0, y = 0, z = 0;
+  int64_t o_row = 0;
   if (live) {
-    const int64_t o = (!MASK_ONLY && order) ? (int64_t)__ldg(order + j) : j;
-    unpack_key(out_keys[o], b, x, y, z);
+    o_row = (!MASK_ONLY && order) ? (int64_t)__ldg(order + j) : j;
+    unpack_key(out_keys[o_row], b, x, y, z);
   }
   uint32_t mine = 0;
   const int amask = in_align - 1;  // in_align is a power of two
+  // write pass after a mask pass: the row's mask says which neighbours exist, so the (longer) probe sequences
+  // of the missing ones are not walked a second time
+  const uint32_t known = (!MASK_ONLY && row_masks && live) ? __ldg(row_masks + o_row) : 0xffffffffu;
 #pragma unroll 3
   for (int k = 0; k < K; ++k) {
     if (!MASK_ONLY && (k < k_lo || k >= k_hi)) continue;
     const int dx = k % KS + LO, dy = (k / KS) % KS + LO, dz = k / (KS * KS) + LO;
     const int qx = x + dx * step, qy = y + dy * step, qz = z + dz * step;
     int r = -1;
-    if (live && coord_in_range(qx) && coord_in_range(qy) && coord_in_range(qz) &&
+    if (live && ((known >> k) & 1u) && coord_in_range(qx) && coord_in_range(qy) && coord_in_range(qz) &&
         (((qx | qy | qz) & amask) == 0))
       r = hash_find(tkeys, tvals, cap_mask, pack_key(b, qx, qy, qz));
     if (!MASK_ONLY && live) nbr[(int64_t)k * nbr_stride + j] = r;
@@ -630,7 +634,7 @@ static int kernel_map_launch(const uint64_t* tkeys, const int32_t* tvals, uint64
     }
     kernel_map_kernel<KS, false><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align,
                                                              order_g, nbr, nbr_stride,
-                                                             tapmask ? tapmask + (int64_t)g * grid : nullptr, nullptr,
+                                                             tapmask ? tapmask + (int64_t)g * grid : nullptr, row_masks,
                                                              k_lo, k_hi);
     PCC_CHECK_LAUNCH("kernel_map_kernel");
     if (tile_order && tapmask) {
