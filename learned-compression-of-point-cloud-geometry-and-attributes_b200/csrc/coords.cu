@@ -270,12 +270,13 @@ kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict_
 }
 
 // sort key of row j for one offset group: (j / seg_rows, the group's bits of the row's neighbour mask)
+template <typename KeyT>
 __global__ void group_key_kernel(const uint32_t* __restrict__ row_masks, int64_t n, int k_lo, int k_hi, int seg_shift,
-                                 uint64_t* __restrict__ keys, int32_t* __restrict__ iota) {
+                                 KeyT* __restrict__ keys, int32_t* __restrict__ iota) {
   const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n) return;
-  const uint32_t sub = (row_masks[j] >> k_lo) & ((1u << (k_hi - k_lo)) - 1u);
-  keys[j] = ((uint64_t)(j >> seg_shift) << (k_hi - k_lo)) | sub;
+  const uint32_t sub = (row_masks[j] >> k_lo) & (uint32_t)((1ull << (k_hi - k_lo)) - 1ull);
+  keys[j] = (KeyT)(((uint64_t)(j >> seg_shift) << (k_hi - k_lo)) | sub);
   iota[j] = (int32_t)j;
 }
 
@@ -290,6 +291,35 @@ static size_t cub_sort_keys_bytes(int64_t n) {
   size_t bytes = 0;
   cub::DeviceRadixSort::SortKeys(nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr, (int)n);
   return bytes;
+}
+
+// order_out = rows sorted (stably) by the group key.  Keys of <= 32 bits (every whole-map sort: 27 mask bits; the
+// segmented sorts up to 4 M rows) are sorted as 32-bit keys: a third less traffic per radix pass.
+static int sort_rows_by_group_key(const uint32_t* row_masks, int64_t n, int k_lo, int k_hi, int seg_shift, int seg_bits,
+                                  void* k_in, void* k_out, int32_t* iota, int32_t* order_out, void* cub_ws,
+                                  size_t cub_bytes, cudaStream_t st) {
+  const int bits = (k_hi - k_lo) + seg_bits;
+  const unsigned grid = (unsigned)ceil_div(n, 256);
+  if (bits <= 32) {
+    size_t need = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, need, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const int32_t*)nullptr,
+                                    (int32_t*)nullptr, (int)n);
+    if (need <= cub_bytes) {
+      group_key_kernel<uint32_t><<<grid, 256, 0, st>>>(row_masks, n, k_lo, k_hi, seg_shift,
+                                                       reinterpret_cast<uint32_t*>(k_in), iota);
+      PCC_CHECK_LAUNCH("group_key_kernel");
+      PCC_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(cub_ws, cub_bytes, reinterpret_cast<const uint32_t*>(k_in),
+                                                     reinterpret_cast<uint32_t*>(k_out), iota, order_out, (int)n, 0,
+                                                     bits, st));
+      return PCC_OK;
+    }
+  }
+  group_key_kernel<uint64_t><<<grid, 256, 0, st>>>(row_masks, n, k_lo, k_hi, seg_shift,
+                                                   reinterpret_cast<uint64_t*>(k_in), iota);
+  PCC_CHECK_LAUNCH("group_key_kernel");
+  PCC_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(cub_ws, cub_bytes, reinterpret_cast<const uint64_t*>(k_in),
+                                                 reinterpret_cast<uint64_t*>(k_out), iota, order_out, (int)n, 0, bits, st));
+  return PCC_OK;
 }
 
 static int sort_keys_only(const uint64_t* in, uint64_t* out, int64_t n, void* ws, size_t ws_bytes,
@@ -607,10 +637,11 @@ static int kernel_map_launch(const uint64_t* tkeys, const int32_t* tvals, uint64
     // sort by the whole mask, measure how well such tiles would be used, decide
     unsigned long long* sums = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(cub_ws) + cub_bytes);
     PCC_CHECK_CUDA(cudaMemsetAsync(sums, 0, 16, st));
-    group_key_kernel<<<grid_for(n_out), THREADS, 0, st>>>(row_masks, n_out, 0, K, seg_shift, k_in, iota);
-    PCC_CHECK_LAUNCH("group_key_kernel");
-    PCC_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(cub_ws, cub_bytes, k_in, k_out, iota, order, (int)n_out, 0,
-                                                   K + seg_bits, st));
+    {
+      const int rc = sort_rows_by_group_key(row_masks, n_out, 0, K, seg_shift, seg_bits, k_in, k_out, iota, order,
+                                            cub_ws, cub_bytes, st);
+      if (rc) return rc;
+    }
     tile_efficiency_kernel<<<grid, PCC_TILE_M, 0, st>>>(row_masks, order, n_out, sums);
     PCC_CHECK_LAUNCH("tile_efficiency_kernel");
     unsigned long long hbuf[2] = {0, 0};
@@ -627,10 +658,9 @@ static int kernel_map_launch(const uint64_t* tkeys, const int32_t* tvals, uint64
     const int k_lo = g * per, k_hi = (g + 1) * per < K ? (g + 1) * per : K;
     int32_t* order_g = order + (int64_t)g * n_out;
     if (!have_order0) {
-      group_key_kernel<<<grid_for(n_out), THREADS, 0, st>>>(row_masks, n_out, k_lo, k_hi, seg_shift, k_in, iota);
-      PCC_CHECK_LAUNCH("group_key_kernel");
-      PCC_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(cub_ws, cub_bytes, k_in, k_out, iota, order_g, (int)n_out, 0,
-                                                     (k_hi - k_lo) + seg_bits, st));
+      const int rc = sort_rows_by_group_key(row_masks, n_out, k_lo, k_hi, seg_shift, seg_bits, k_in, k_out, iota,
+                                            order_g, cub_ws, cub_bytes, st);
+      if (rc) return rc;
     }
     kernel_map_kernel<KS, false><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align,
                                                              order_g, nbr, nbr_stride,
