@@ -18,7 +18,8 @@ def _run(*args, env=None):
 
 
 def test_reference_arm_prints_one_contract_line():
-    r = _run("--impl", "reference", "--steps", "1", "--warmup", "0", "--cpu-radius", "14")
+    r = _run("--impl", "reference", "--steps", "2", "--warmup", "1", "--radius", "14", "--grid", "128", "--cpu-radius", "10",
+             env={"OMP_NUM_THREADS": "1"})  # what torchrun exports: the arm must not inherit it
     assert r.returncode == 0, r.stderr[-2000:]
     lines = [l for l in r.stdout.splitlines() if l.strip()]
     assert len(lines) == 1
@@ -28,12 +29,14 @@ def test_reference_arm_prints_one_contract_line():
         assert k in d, k
     assert d["impl"] == "reference" and d["unit"] == "points/s" and d["higher_is_better"] is True
     assert d["value"] > 0 and d["vs_baseline"] is None and "workload" in d["config"]
-    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
+    assert d["cpu_baseline"]["kind"] == "port"
+    assert d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))   # all host threads, whatever OMP_NUM_THREADS says
+    assert d["steps"] == 2 and d["warmup"] == 1 and "value_100k_frame" in d["cpu_baseline"]
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
 
 
 def test_reference_arm_other_ranks_exit_quietly():
-    r = _run("--impl", "reference", "--steps", "1", "--warmup", "0", "--cpu-radius", "14", "--gpus", "2",
+    r = _run("--impl", "reference", "--steps", "1", "--warmup", "0", "--radius", "14", "--grid", "128", "--gpus", "2",
              env={"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"})
     assert r.returncode == 0 and r.stdout.strip() == ""
 
