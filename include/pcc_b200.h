@@ -276,6 +276,19 @@ int pcc_scatter_rows_add(const float* g, int32_t c, const int32_t* rows, int64_t
  * row-major [n x c] matrix, c <= 1024; fixed summation order (deterministic).  ws: pcc_col_sum_ws_bytes(c). */
 size_t pcc_col_sum_ws_bytes(int32_t c);
 int pcc_col_sum(const float* in, int64_t n, int32_t c, float* out, void* ws, size_t ws_bytes, void* stream);
+/* pcc_col_sum for callers that must not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same kernels and the same bits as pcc_col_sum, but the block partials live in a file-scope
+ * `static __device__` array inside the library instead of a caller workspace: every GPU that loads the
+ * library holds its 592 x PCC_COL_SUM_STATIC_MAX_C x 4 = 606,208 bytes until the process exits.
+ * The call itself allocates nothing (no cudaMalloc / cudaFree / allocating library routine); the array's
+ * device address is looked up once per device (cudaGetSymbolAddress, with that device current).
+ * c > PCC_COL_SUM_STATIC_MAX_C is rejected with PCC_ERR_CAPACITY and a message naming the limit.
+ * Every call on a device shares the one array: calls whose kernels may overlap on the GPU (different
+ * streams without an ordering between them) RACE on it — order them, or use pcc_col_sum with separate
+ * workspaces.  Nothing in the array has to start at zero (each call overwrites what it reads). */
+#define PCC_COL_SUM_STATIC_MAX_C 256
+int pcc_col_sum_static(const float* in, int64_t n, int32_t c, float* out, void* stream);
 /* GaussianConditional.forward(training=True) (model/entropy_models.py:330 in train mode): y_noisy =
  * y + U(-0.5, 0.5) is made by the caller; likelihood [n x c] row-major = max(Phi((0.5 - v) / s) -
  * Phi((-0.5 - v) / s), likelihood_bound), v = |y_noisy - mean|, s = max(scale, scale_bound).  The

@@ -80,6 +80,7 @@ SIGNATURES = {
     "pcc_scatter_rows_add": (I32, [P, I32, P, I64, P, P]),
     "pcc_col_sum_ws_bytes": (SZ, [I32]),
     "pcc_col_sum": (I32, [P, I64, I32, P, P, SZ, P]),
+    "pcc_col_sum_static": (I32, [P, I64, I32, P, P]),
     "pcc_gc_likelihood_train_fwd": (I32, [P, P, P, I64, I32, F32, F32, P, P]),
     "pcc_gc_likelihood_train_bwd": (I32, [P, P, P, I64, I32, F32, F32, P, P, P, P]),
     "pcc_octree_ws_bytes": (SZ, [I64]),

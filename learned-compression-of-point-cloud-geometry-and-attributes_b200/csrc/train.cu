@@ -15,6 +15,7 @@
 #include "pcc_common.cuh"
 
 #include <algorithm>
+#include <mutex>
 
 namespace pcc {
 
@@ -373,6 +374,44 @@ bool wgrad_tf32_supported(const pcc_wgrad_args* a);
 int wgrad_tf32(const pcc_wgrad_args* a, int* splits, cudaStream_t st);
 }  // namespace pcc
 
+namespace pcc {
+// ---------------------------------------------------------------- pcc_col_sum without any allocation
+// Same two kernels as pcc_col_sum, but the block partials live in a file-scope device array instead of a
+// caller-supplied workspace, for callers that may not allocate (CUDA graph capture, serving loops).
+// The array is part of the module image: every GPU that loads the library holds its 606,208 bytes until the
+// process exits.  `g_colsum_static_scratch` in HOST code is only a handle for the runtime's symbol table, not
+// a device address; the address is asked for once per device with cudaGetSymbolAddress and cached.
+constexpr int COLSUM_STATIC_MAX_C = PCC_COL_SUM_STATIC_MAX_C;
+static __device__ __align__(256) float g_colsum_static_scratch[COLSUM_BLOCKS * COLSUM_STATIC_MAX_C];
+
+constexpr int COLSUM_MAX_DEVICES = 64;
+
+// Device address of the scratch array on the CURRENT device (looked up on first use on that device).
+int colsum_static_scratch(float** out) {
+  static std::mutex mu;
+  static float* addr[COLSUM_MAX_DEVICES] = {};
+  int dev = -1;
+  PCC_CHECK_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= COLSUM_MAX_DEVICES) {
+    set_error("pcc_col_sum_static: device ordinal %d outside the supported range [0, %d)", dev, COLSUM_MAX_DEVICES);
+    return PCC_ERR_INVALID_ARG;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    PCC_CHECK_CUDA(cudaGetSymbolAddress(&p, g_colsum_static_scratch));
+    if (!p) {
+      set_error("pcc_col_sum_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+      return PCC_ERR_CUDA;
+    }
+    addr[dev] = static_cast<float*>(p);
+  }
+  *out = addr[dev];
+  return PCC_OK;
+}
+
+}  // namespace pcc
+
 using namespace pcc;
 
 extern "C" {
@@ -448,6 +487,34 @@ int pcc_col_sum(const float* in, int64_t n, int32_t c, float* out, void* ws, siz
   PCC_CHECK_LAUNCH("col_sum_partial_kernel");
   col_sum_final_kernel<<<(unsigned)ceil_div(c, 128), 128, 0, st>>>(reinterpret_cast<const float*>(ws), blocks, c, out);
   PCC_CHECK_LAUNCH("col_sum_final_kernel");
+  return PCC_OK;
+}
+
+int pcc_col_sum_static(const float* in, int64_t n, int32_t c, float* out, void* stream) {
+  PCC_REQUIRE(out && c > 0 && n >= 0, "bad argument");
+  if (c > COLSUM_STATIC_MAX_C) {
+    set_error("pcc_col_sum_static: c = %d exceeds the static scratch limit PCC_COL_SUM_STATIC_MAX_C = %d columns "
+              "(use pcc_col_sum with a caller workspace)", (int)c, COLSUM_STATIC_MAX_C);
+    return PCC_ERR_CAPACITY;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n == 0) {
+    PCC_CHECK_CUDA(cudaMemsetAsync(out, 0, (size_t)c * sizeof(float), st));
+    return PCC_OK;
+  }
+  PCC_REQUIRE(in, "null input");
+  float* scratch = nullptr;
+  const int rc = colsum_static_scratch(&scratch);
+  if (rc != PCC_OK) return rc;
+  // Nothing has to start at zero: every block 0..blocks-1 overwrites all c entries of its partial row before
+  // col_sum_final_kernel reads exactly those blocks x c entries; what an earlier call left beyond them is not read.
+  const bool vec = (c % 4 == 0) && ((reinterpret_cast<uintptr_t>(in) & 15) == 0);
+  const int blocks = (int)std::min<int64_t>(COLSUM_BLOCKS, ceil_div(n, 64));
+  if (vec) col_sum_partial_kernel<4><<<blocks, 256, 0, st>>>(in, n, c, scratch);
+  else col_sum_partial_kernel<1><<<blocks, 256, 0, st>>>(in, n, c, scratch);
+  PCC_CHECK_LAUNCH("col_sum_partial_kernel (static scratch)");
+  col_sum_final_kernel<<<(unsigned)ceil_div(c, 128), 128, 0, st>>>(scratch, blocks, c, out);
+  PCC_CHECK_LAUNCH("col_sum_final_kernel (static scratch)");
   return PCC_OK;
 }
 
