@@ -6,6 +6,8 @@ Control flow of the reference's encode/decode path restated over ``oracle.prims`
   AnalysisTransform / SparseSynthesisTransform /root/reference/model/transforms.py
   ScaledBlock / GenerativeUpBlock / ConditionEncoder /root/reference/model/blocks.py
   MeanScaleHyperprior_Map                      /root/reference/model/entropy_models.py:253-414
+  MeanScaleHyperprior (two-model variant)      /root/reference/model/entropy_models.py:104-250,
+                                               selected by model/model.py:22-27,131-135,196-200
 
 ``params`` maps the reference's state_dict names (e.g. ``g_a.pre_conv.0.kernel``) to numpy
 arrays: ME kernel layout [K, Cin, Cout] ([Cin, Cout] for kernel_size 1), bias [1, Cout].
@@ -26,9 +28,14 @@ class OracleCodec:
         self.src_cond_gs = bool(config["g_s"]["source_condition"])
         self.dense = config["g_s"].get("dense", True)
         # ColorModel.update -> CompressionModel.update(force=True) (model/model.py:30-36)
-        eb = {k.split(".")[-1]: v for k, v in self.p.items()
-              if k.startswith("entropy_model.entropy_bottleneck.")}
-        self.eb = EntropyBottleneckOracle(eb)
+        # "entropy_model_map" in the config (model/model.py:22-27): y and the latent quality map are coded by
+        # two MeanScaleHyperprior models (no h_q) instead of one MeanScaleHyperprior_Map
+        self.two_models = "entropy_model_map" in config
+        self.ebs = {}
+        for prefix in ("entropy_model", "entropy_model_map") if self.two_models else ("entropy_model",):
+            eb = {k.split(".")[-1]: v for k, v in self.p.items() if k.startswith(prefix + ".entropy_bottleneck.")}
+            self.ebs[prefix] = EntropyBottleneckOracle(eb)
+        self.eb = self.ebs["entropy_model"]
         self.gc = GaussianConditionalOracle()
         self.trace = {}
 
@@ -168,8 +175,8 @@ class OracleCodec:
         return x
 
     # ---------------------------------------------------------------- entropy_models.py
-    def h_a(self, y):
-        P = "entropy_model.h_a"
+    def h_a(self, y, model="entropy_model"):
+        P = model + ".h_a"
         z = self._conv(y, P + ".0", 3)
         z = z.with_feats(leaky_relu(z.F))
         z = self._conv(z, P + ".2", 3, 2)
@@ -178,10 +185,10 @@ class OracleCodec:
         z = self._conv(z, P + ".5", 3, 2)
         return self._conv(z, P + ".6", 3)
 
-    def h_s(self, z_hat):
-        """h_s (model/entropy_models.py:284-294); the Sorted* shims (:12-102) only permute rows
+    def h_s(self, z_hat, model="entropy_model"):
+        """h_s (model/entropy_models.py:284-294, :135-145); the Sorted* shims (:12-102) only permute rows
         into canonical order, which every oracle tensor already has."""
-        P = "entropy_model.h_s"
+        P = model + ".h_s"
         g = self._conv(z_hat, P + ".0", 3)
         g = self._convT(g, P + ".1", 2)
         g = g.with_feats(leaky_relu(g.F))
@@ -202,33 +209,37 @@ class OracleCodec:
         q = q.with_feats(relu(q.F))
         return self._conv(q, P + ".6", 3)
 
-    def _gaussian_params(self, z_hat, y_coords):
-        gp = features_at(self.h_s(z_hat), y_coords)
+    def _gaussian_params(self, z_hat, y_coords, model="entropy_model"):
+        gp = features_at(self.h_s(z_hat, model), y_coords)
         half = gp.shape[1] // 2
         return gp[:, :half].T.copy(), gp[:, half:].T.copy()  # scales, means as [C, N]
 
-    def entropy_compress(self, y):
-        """MeanScaleHyperprior_Map.compress (model/entropy_models.py:341-381)."""
-        z = self.h_a(y)  # y, z already canonical (sort_tensor, :346-347)
+    def entropy_compress(self, y, model="entropy_model"):
+        """MeanScaleHyperprior_Map.compress (model/entropy_models.py:341-381) and MeanScaleHyperprior.compress
+        (:179-218): the same statements, the second class only lacks h_q."""
+        eb = self.ebs[model]
+        z = self.h_a(y, model)  # y, z already canonical (sort_tensor, :346-347 / :184-185)
         shape = [z.n]
-        z_string = self.eb.compress(z.F.T)
-        z_hat_feats = self.eb.decompress(z_string, shape[0])  # (:353) decode again to get z_hat
+        z_string = eb.compress(z.F.T)
+        z_hat_feats = eb.decompress(z_string, shape[0])  # (:353 / :191) decode again to get z_hat
         z_hat = OT(z.C, z_hat_feats.T, 32, _sorted=True)
-        scales, means = self._gaussian_params(z_hat, y.C)
+        scales, means = self._gaussian_params(z_hat, y.C, model)
         indexes = self.gc.build_indexes(scales)
         y_string = self.gc.compress(y.F.T, indexes, means)
-        self.trace.update(z=z, z_hat=z_hat, scales=scales, means=means, indexes=indexes,
-                          y_symbols=self.gc.quantize(y.F.T, means),
-                          z_symbols=np.rint(z.F.T - self.eb.medians()[:, None]).astype(np.int32))
+        sfx = "" if model == "entropy_model" else "_map"
+        self.trace.update({"z" + sfx: z, "z_hat" + sfx: z_hat, "scales" + sfx: scales, "means" + sfx: means,
+                           "indexes" + sfx: indexes, "y_symbols" + sfx: self.gc.quantize(y.F.T, means),
+                           "z_symbols" + sfx: np.rint(z.F.T - eb.medians()[:, None]).astype(np.int32)})
         return [y.C, z.C], [[y_string], [z_string]], shape
 
-    def entropy_decompress(self, points, strings, shape):
-        """MeanScaleHyperprior_Map.decompress (model/entropy_models.py:384-414)."""
-        y_points = prims.unpack_keys(np.sort(prims.pack_keys(points[0])))  # sort_points (:389-390)
+    def entropy_decompress(self, points, strings, shape, model="entropy_model", with_h_q=True):
+        """MeanScaleHyperprior_Map.decompress (model/entropy_models.py:384-414) -> (y_hat, Q_hat);
+        MeanScaleHyperprior.decompress (:221-250, with_h_q=False) -> (y_hat, None)."""
+        y_points = prims.unpack_keys(np.sort(prims.pack_keys(points[0])))  # sort_points (:389-390 / :226-227)
         z_points = prims.unpack_keys(np.sort(prims.pack_keys(points[1])))
-        z_hat = OT(z_points, self.eb.decompress(strings[1][0], shape[0]).T, 32, _sorted=True)
-        Q_hat = self.h_q(z_hat)
-        scales, means = self._gaussian_params(z_hat, y_points)
+        z_hat = OT(z_points, self.ebs[model].decompress(strings[1][0], shape[0]).T, 32, _sorted=True)
+        Q_hat = self.h_q(z_hat) if with_h_q else None
+        scales, means = self._gaussian_params(z_hat, y_points, model)
         indexes = self.gc.build_indexes(scales)
         y_hat = OT(y_points, self.gc.decompress(strings[0][0], indexes, means).T, 8, _sorted=True)
         return y_hat, Q_hat
@@ -253,8 +264,14 @@ class OracleCodec:
         inp = OT(points, feats, 1)
         Q = OT(Q_coords, Q_feats, 1)
         y, Q, k = self.g_a(inp, Q)
-        self.trace.update(y=y)
-        points, strings, shape = self.entropy_compress(y)
+        self.trace.update(y=y, Q_latent=Q)
+        if not self.two_models:
+            points, strings, shape = self.entropy_compress(y)
+        else:  # model/model.py:131-135
+            points, y_strings, y_shape = self.entropy_compress(y, "entropy_model")
+            _, Q_strings, Q_shape = self.entropy_compress(Q, "entropy_model_map")
+            strings = [y_strings, Q_strings]
+            shape = [y_shape, Q_shape]
         return strings, shape, k, y.C
 
     def decompress(self, coordinates, strings, shape, k):
@@ -262,7 +279,12 @@ class OracleCodec:
         lat = OT(coordinates, np.ones((coordinates.shape[0], 1), np.float32), 8)
         W = self.p["g_s.down_conv.kernel"]
         lat = conv(conv(lat, W, None, 3, 2), W, None, 3, 2)  # only .C is used (:188-191)
-        y_hat, Q_hat = self.entropy_decompress([coordinates, lat.C], strings, shape)
+        if not self.two_models:
+            y_hat, Q_hat = self.entropy_decompress([coordinates, lat.C], strings, shape)
+        else:  # model/model.py:196-200
+            points = [coordinates, lat.C]
+            y_hat, _ = self.entropy_decompress(points, strings[0], shape[0], "entropy_model", with_h_q=False)
+            Q_hat, _ = self.entropy_decompress(points, strings[1], shape[1], "entropy_model_map", with_h_q=False)
         self.trace.update(y_hat=y_hat, Q_hat=Q_hat)
         x_hat = self.g_s(y_hat, Q_hat, k)
         feats = np.clip(np.rint(x_hat.F * np.float32(255)), 0.0, 255.0).astype(np.float32) / np.float32(255)

@@ -119,8 +119,14 @@ SCALE_MIN, SCALE_MAX, SCALE_LEVELS = 0.11, 256.0, 64
 
 
 def get_scale_table():
-    """compressai.models.utils.get_scale_table: exp(linspace(log .11, log 256, 64)) as float32."""
-    return np.exp(np.linspace(np.log(SCALE_MIN), np.log(SCALE_MAX), SCALE_LEVELS)).astype(np.float32)
+    """compressai.models.utils.get_scale_table, literally: ``torch.exp(torch.linspace(math.log(min),
+    math.log(max), levels))`` — float32 linspace and float32 exp IN TORCH.  A float64 numpy evaluation rounded to
+    float32 differs from it in the last bit of 46 of the 64 entries, and a scale that falls between the two
+    versions of a threshold then gets a different CDF index: found by the full-frame parity test
+    (tests/test_gpu_baseline_sizes.py: 1 index of 2.3 M on the 799,458-point ablation frame)."""
+    import math
+    import torch
+    return torch.exp(torch.linspace(math.log(SCALE_MIN), math.log(SCALE_MAX), SCALE_LEVELS)).numpy().astype(np.float32)
 
 
 class GaussianConditionalOracle:

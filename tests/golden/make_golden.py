@@ -32,7 +32,13 @@ CASES = [  # name, yaml, product config name, shell radius, seed, (q_g, q_a), no
     # view-dependent gradient along y and region of interest beyond x = 64 (evaluate_view_dep.py:209-216,252-258)
     ("ours_r13_view", "configs/Ours.yaml", "OURS_CONFIG", 13.0, 4, (0.8, 1.0), ("view", 1, 52.0, 76.0)),
     ("ours_r12_roi", "configs/Ours.yaml", "OURS_CONFIG", 12.0, 5, (1.0, 0.6), ("roi", 0, 64.0)),
+    # ColorModel.__init__ with an "entropy_model_map" section (model/model.py:22-27): two MeanScaleHyperprior models
+    # (model/entropy_models.py:104-250) code y and the latent quality map separately.  No shipped YAML has the
+    # section; it is added to Ours.yaml's `model:` here and stored in the fixture as JSON.
+    ("twohyper_r13", "configs/Ours.yaml", "OURS_CONFIG", 13.0, 6, (0.4, 0.8), None),
 ]
+EXTRA = {"twohyper_r13": {"entropy_model": {"C_bottleneck": 128, "C_hyper_bottleneck": 128},
+                          "entropy_model_map": {"C_bottleneck": 2, "C_hyper_bottleneck": 8}}}
 
 
 def quality_features(x, q, kind):
@@ -51,12 +57,25 @@ def quality_features(x, q, kind):
     return torch.cat([torch.tensor(q_map_g), torch.tensor(q_map_a)], dim=1).type(torch.float32)  # utils.py:442
 
 
+def string_fields(name, cfg, strings, shape):
+    """One hyperprior: strings = [[y], [z]], shape = [N_z].  Two (model/model.py:131-135): strings =
+    [[[y], [z]], [[y_map], [z_map]]], shape = [[N_z], [N_z_map]]; the config goes along as JSON."""
+    import json
+    u8 = lambda b: np.frombuffer(b, np.uint8)
+    if "entropy_model_map" not in cfg:
+        return dict(y_string=u8(strings[0][0]), z_string=u8(strings[1][0]), shape=np.array(shape, np.int64))
+    return dict(y_string=u8(strings[0][0][0]), z_string=u8(strings[0][1][0]), y_map_string=u8(strings[1][0][0]),
+                z_map_string=u8(strings[1][1][0]), shape=np.array([shape[0][0], shape[1][0]], np.int64),
+                config_json=np.array(json.dumps(cfg)))
+
+
 def main():
     import pcc_b200
     from oracle import ref_shims
     for name, yml, cfg_name, radius, seed, q, kind in CASES:
         cfg = yaml.safe_load(open(os.path.join(REF, yml)))["model"]
         assert cfg == getattr(pcc_b200, cfg_name), f"{yml} differs from pcc_b200.{cfg_name}"
+        cfg.update(EXTRA.get(name, {}))
         ref_model = ref_shims.load_reference_model(cfg, REF)
         # deterministic synthetic weights, taken through the state_dict so key names are pinned
         ours = pcc_b200.ColorModel(cfg)
@@ -88,10 +107,9 @@ def main():
             config=cfg_name, radius=radius, seed=seed, q=np.array(q, np.float32),
             x=x.numpy().astype(np.float32), qf=qf.numpy().astype(np.float32),
             qkind=np.array([] if kind is None else [{"view": 0.0, "roi": 1.0}[kind[0]]] + [float(v) for v in kind[1:]]),
-            y_string=np.frombuffer(strings[0][0], np.uint8), z_string=np.frombuffer(strings[1][0], np.uint8),
-            shape=np.array(shape, np.int64), k=np.array([int(kk[0]) for kk in k], np.int64),
-            coordinates=coords, out=out.astype(np.float32))
-        print(f"{name}: {x.shape[0]} points, y/z bytes {len(strings[0][0])}/{len(strings[1][0])}, "
+            k=np.array([int(kk[0]) for kk in k], np.int64), coordinates=coords, out=out.astype(np.float32),
+            **string_fields(name, cfg, strings, shape))
+        print(f"{name}: {x.shape[0]} points, string bytes {[[len(b[0]) for b in s] if isinstance(s[0], list) else len(s[0]) for s in strings]}, "
               f"shape {shape}, k {k}, latent voxels {coords.shape[0]}, decoded {out.shape}")
         for m in [m for m in sys.modules if m == "model" or m.startswith("model.") or m == "utils"]:
             del sys.modules[m]

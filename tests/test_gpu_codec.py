@@ -114,30 +114,44 @@ def test_prune_before_refine_variant_bit_exact(pcc, oracle):
     assert np.array_equal(out.cpu().numpy(), o_out)
 
 
-def test_two_hyperprior_variant_round_trip(pcc):
+def test_two_hyperprior_variant_bit_exact(pcc, oracle):
     """``entropy_model_map`` in the config (model/model.py:22-27,131-135,196-200): y and the latent quality
     map are coded by two independent MeanScaleHyperprior models (model/entropy_models.py:104-250).  No
-    shipped config selects it and the oracle does not restate it, so this is the domain's round-trip
-    property: the decoder recovers exactly the encoder's quantised latents, for both streams."""
+    shipped config selects it; the oracle restates it (oracle/codec.py, pinned by the reference-code fixture
+    tests/golden/twohyper_r13.npz) and the CUDA path must agree bit for bit, both streams."""
     import copy
     config = copy.deepcopy(pcc.OURS_CONFIG)
     config["entropy_model"] = {"C_bottleneck": 128, "C_hyper_bottleneck": 128}
     config["entropy_model_map"] = {"C_bottleneck": 2, "C_hyper_bottleneck": 8}
     model = pcc.ColorModel(config)
     pcc.codec.init_synthetic(model, 3)
-    model.eval().to(DEV)
+    model.eval()
+    params = pcc.codec.export_params(model)
+    model.to(DEV)
     model.update()
     assert not hasattr(model.entropy_model, "h_q") and not hasattr(model.entropy_model_map, "h_q")
     x = pcc.synthetic.shell_frame(20.0, center=[64] * 3, grid=128, seed=3)
     qc, qf = pcc.synthetic.uniform_q_map(x, 0.5, 0.5)
     strings, shape, k, coords = model.compress(x.to(DEV), (qc.to(DEV), qf.to(DEV)))
     assert len(strings) == 2 and len(shape) == 2 and all(len(s) == 2 for s in strings)
+    oc = oracle.OracleCodec(params, config)
+    o_strings, o_shape, o_k, o_coords = oc.compress(x.numpy(), qc.numpy(), qf.numpy())
+    assert strings == o_strings and shape == o_shape and k == o_k
+    assert np.array_equal(coords.cpu().numpy(), o_coords)
+    for em, sfx in ((model.entropy_model, ""), (model.entropy_model_map, "_map")):
+        assert np.array_equal(em.last["y_symbols"].cpu().numpy(), oc.trace["y_symbols" + sfx])
+        assert np.array_equal(em.last["indexes"].cpu().numpy(), oc.trace["indexes" + sfx])
+        assert np.array_equal(em.last["z_symbols"].cpu().numpy(), oc.trace["z_symbols" + sfx])
     enc = []
     for em in (model.entropy_model, model.entropy_model_map):
         last = em.last
         enc.append(last["y_symbols"].t().float() + last["params"].F[:, last["params"].F.shape[1] // 2:])
     out = model.decompress(coordinates=coords, strings=strings, shape=shape, k=k)
+    o_out = oc.decompress(o_coords, o_strings, o_shape, o_k)
     assert out.shape == (x.shape[0], 6)
+    assert np.array_equal(out.cpu().numpy().view(np.uint32), o_out.view(np.uint32))
+    assert np.array_equal(model.last["y_hat"].F.cpu().numpy(), oc.trace["y_hat"].F)
+    assert np.array_equal(model.last["Q_hat"].F.cpu().numpy().view(np.uint32), oc.trace["Q_hat"].F.view(np.uint32))
     assert torch.equal(model.last["y_hat"].F, enc[0])
     assert torch.equal(model.last["Q_hat"].F, enc[1])
     assert model.last["Q_hat"].F.shape[1] == 2

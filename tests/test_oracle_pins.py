@@ -153,3 +153,19 @@ def test_topk_tie_break_convention(oracle):
     assert np.nonzero(oracle.prims.topk_mask(v, 2))[0].tolist() == [1, 2]
     assert np.nonzero(oracle.prims.topk_mask(v, 5))[0].tolist() == [0, 1, 2, 3, 4]
     assert np.nonzero(oracle.prims.topk_mask(v, 6))[0].tolist() == [0, 1, 2, 3, 4, 6]  # +0 outranks -0
+
+
+def test_scale_table_is_compressai_formula(pcc, oracle):
+    """compressai.models.utils.get_scale_table is torch.exp(torch.linspace(log .11, log 256, 64)) in float32;
+    the oracle and the product must both use exactly that (a float64 evaluation differs in the last bit of
+    most entries, which moved one CDF index on the 799,458-point ablation frame)."""
+    import math
+    import torch
+    want = torch.exp(torch.linspace(math.log(0.11), math.log(256), 64))
+    assert np.array_equal(oracle.entropy.get_scale_table().view(np.uint32), want.numpy().view(np.uint32))
+    assert torch.equal(pcc.compressai_compat.get_scale_table(), want)
+    m = pcc.ColorModel(pcc.OURS_CONFIG)
+    m.update()
+    assert torch.equal(m.entropy_model.gaussian_conditional.scale_table, want)
+    assert np.array_equal(oracle.entropy.GaussianConditionalOracle().quantized_cdf,
+                          m.entropy_model.gaussian_conditional._quantized_cdf.numpy())
