@@ -88,6 +88,8 @@ def apply_conv(x, layer, out_map=None, transpose=False, **epilogue):
                                  transpose=transpose, **epilogue), out_map)
     if isinstance(x.m, SlabMap):  # one slab of a partitioned scene: owned rows computed, halo rows exchanged
         return ST(x.m.conv(x.F, out_map, layer, transpose, epilogue), out_map)
+    if x.F.shape[0] != x.m.n:  # the kernels index rows by the map: a shorter matrix would be read out of bounds
+        raise PccError(f"feature matrix has {x.F.shape[0]} rows, its coordinate map {x.m.n}")
     kmap = x.m.kernel_map(out_map, layer.kernel_size, transpose=transpose)
     return ST(ops.conv(x.F, kmap, layer.kernel, layer.bias, **epilogue), out_map)
 
@@ -237,9 +239,17 @@ class GenerativeUpBlock(nn.Module):
             nb = cand_map.n_batches if cand_map.n else 0
         else:
             nb = int((cand_map.keys[-1] >> 48).item()) + 1 if cand_map.n else 0
+        if len(k) < max(nb, 1):
+            raise PccError(f"corrupt stream: {len(k)} point counts for {nb} batch elements")
         if nb <= 1:
+            if not 0 <= int(k[0]) <= cand_map.n:
+                raise PccError(f"corrupt stream: point count {int(k[0])} exceeds the {cand_map.n} candidate voxels of its stage")
             return ops.topk_rows(logits, int(k[0]))
         bounds = torch.searchsorted(cand_map.keys >> 48, torch.arange(nb + 1, device=logits.device)).tolist()
+        for b in range(nb):
+            if not 0 <= int(k[b]) <= bounds[b + 1] - bounds[b]:
+                raise PccError(f"corrupt stream: point count {int(k[b])} of batch element {b} exceeds its "
+                               f"{bounds[b + 1] - bounds[b]} candidate voxels")
         sel = [ops.topk_rows(logits[bounds[b]:bounds[b + 1]], int(k[b])) + bounds[b] for b in range(nb)]
         return torch.cat(sel).to(torch.int32)
 
@@ -526,6 +536,9 @@ class MeanScaleHyperprior_Map(CompressionModel):
     def decompress_gen(self, points, strings, shape):
         """(:384-414).  points = [y map, z map], both canonical (sort_points, :389-390)."""
         y_map, z_map = points
+        n_z = int(shape[0]) if isinstance(shape, (list, tuple)) else int(shape)
+        if n_z != z_map.n:  # a truncated / tampered header must not size tensors the kernels index by the map
+            raise PccError(f"corrupt stream: header says {n_z} hyper-latent rows, the latent coordinates give {z_map.n}")
         with stage("dec.z_coder"):
             z_hat_cn = self.entropy_bottleneck.decompress(strings[1], shape)
             z_hat = ST(z_hat_cn[0].t().contiguous(), z_map)

@@ -11,6 +11,7 @@ reference's sequential CPU algorithm (csrc/host_coder.cpp) and its time is accum
 ``coder_stats`` so callers can report it separately from the GPU path.
 """
 import math
+import threading
 import time
 
 import numpy as np
@@ -24,9 +25,19 @@ coder_stats = {"encode_s": 0.0, "decode_s": 0.0, "d2h_s": 0.0, "h2d_s": 0.0, "sy
                "d2h_bytes": 0, "h2d_bytes": 0}
 
 
+_stats_lock = threading.Lock()
+
+
+def _stat(key, value):
+    """coder_stats is updated from the launch and coder threads of every in-flight frame."""
+    with _stats_lock:
+        coder_stats[key] += value
+
+
 def reset_coder_stats():
-    for k in coder_stats:
-        coder_stats[k] = 0 if isinstance(coder_stats[k], int) else 0.0
+    with _stats_lock:
+        for k in coder_stats:
+            coder_stats[k] = 0 if isinstance(coder_stats[k], int) else 0.0
 
 
 def get_scale_table(min=0.11, max=256, levels=64):
@@ -119,14 +130,17 @@ def drive(gen):
 
 
 _pinned_free = {}
+_pinned_lock = threading.Lock()  # launch threads and coder threads of several in-flight frames share the pool
 
 
 def _pinned(shape, dtype):
     """Page-locked host tensor from a free-list (cudaHostAlloc is far too slow for the hot path)."""
     key = (tuple(shape), dtype)
-    lst = _pinned_free.get(key)
-    if lst:
-        t, ev = lst.pop()
+    with _pinned_lock:
+        lst = _pinned_free.get(key)
+        hit = lst.pop() if lst else None
+    if hit is not None:
+        t, ev = hit
         if ev is not None:
             ev.synchronize()
         return t
@@ -134,7 +148,8 @@ def _pinned(shape, dtype):
 
 
 def _pinned_release(t, after_event=None):
-    _pinned_free.setdefault((tuple(t.shape), t.dtype), []).append((t, after_event))
+    with _pinned_lock:
+        _pinned_free.setdefault((tuple(t.shape), t.dtype), []).append((t, after_event))
 
 
 def _d2h_async(*tensors):
@@ -143,7 +158,7 @@ def _d2h_async(*tensors):
     for t in tensors:
         h = _pinned(t.shape, t.dtype)
         h.copy_(t, non_blocking=True)
-        coder_stats["d2h_bytes"] += h.numel() * h.element_size()
+        _stat("d2h_bytes", h.numel() * h.element_size())
         outs.append(h)
     ev = torch.cuda.Event()
     ev.record()
@@ -158,7 +173,7 @@ def _h2d_async(a, device):
     ev = torch.cuda.Event()
     ev.record()
     _pinned_release(h, ev)
-    coder_stats["h2d_bytes"] += a.nbytes
+    _stat("h2d_bytes", a.nbytes)
     return t
 
 
@@ -174,16 +189,16 @@ def _rows_cn(x):
 def _to_host(t):
     t0 = time.perf_counter()
     a = t.cpu().numpy()
-    coder_stats["d2h_s"] += time.perf_counter() - t0
-    coder_stats["d2h_bytes"] += a.nbytes
+    _stat("d2h_s", time.perf_counter() - t0)
+    _stat("d2h_bytes", a.nbytes)
     return a
 
 
 def _to_dev(a, device):
     t0 = time.perf_counter()
     t = torch.from_numpy(a).to(device)
-    coder_stats["h2d_s"] += time.perf_counter() - t0
-    coder_stats["h2d_bytes"] += a.nbytes
+    _stat("h2d_s", time.perf_counter() - t0)
+    _stat("h2d_bytes", a.nbytes)
     return t
 
 
@@ -199,6 +214,26 @@ class EntropyModel(nn.Module):
         self.register_buffer("_quantized_cdf", torch.IntTensor())
         self.register_buffer("_cdf_length", torch.IntTensor())
         self._host_tables = None
+        self._dev_cache = {}
+
+    _resizable_buffers = ("_offset", "_quantized_cdf", "_cdf_length")
+
+    def _load_from_state_dict(self, state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys,
+                              error_msgs):
+        """CompressAI's ``update_registered_buffers`` (compressai/models/utils.py), done where it cannot be
+        missed: the coder tables are registered empty and get their size in ``update()``, so a checkpoint
+        saved AFTER ``update()`` (the reference's: train.py:291 calls ``model.update()`` before
+        ``state_dict()``, evaluate.py:81 loads that file) carries shapes this module does not have yet.
+        The buffers are re-created with the incoming shapes before the default copy, whatever class the
+        parent model is (this repo's ColorModel or the reference's)."""
+        for name in self._resizable_buffers:
+            src = state_dict.get(prefix + name)
+            buf = getattr(self, name)
+            if src is not None and tuple(src.shape) != tuple(buf.shape):
+                setattr(self, name, torch.empty(tuple(src.shape), dtype=buf.dtype, device=buf.device))
+        super()._load_from_state_dict(state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys,
+                                      error_msgs)
+        self._host_tables = None  # rebuilt from the loaded buffers on first use
         self._dev_cache = {}
 
     def _set_tables(self, cdf, length, offset):
@@ -224,8 +259,8 @@ class EntropyModel(nn.Module):
         cdf, length, offset = self._tables()
         t0 = time.perf_counter()
         s = ops.rans_encode(sym, idx, cdf, length, offset)
-        coder_stats["encode_s"] += time.perf_counter() - t0
-        coder_stats["symbols"] += sym.size
+        _stat("encode_s", time.perf_counter() - t0)
+        _stat("symbols", sym.size)
         return s
 
     def _encode(self, symbols_dev, indexes_dev):
@@ -233,16 +268,16 @@ class EntropyModel(nn.Module):
         cdf, length, offset = self._tables()
         t0 = time.perf_counter()
         s = ops.rans_encode(sym, idx, cdf, length, offset)
-        coder_stats["encode_s"] += time.perf_counter() - t0
-        coder_stats["symbols"] += sym.size
+        _stat("encode_s", time.perf_counter() - t0)
+        _stat("symbols", sym.size)
         return s
 
     def _decode(self, string, indexes_host):
         cdf, length, offset = self._tables()
         t0 = time.perf_counter()
         out = ops.rans_decode(string, indexes_host, cdf, length, offset)
-        coder_stats["decode_s"] += time.perf_counter() - t0
-        coder_stats["symbols"] += out.size
+        _stat("decode_s", time.perf_counter() - t0)
+        _stat("symbols", out.size)
         return out
 
 
@@ -352,8 +387,8 @@ class EntropyBottleneck(EntropyModel):
         cdf, length, offset = self._tables()
         t0 = time.perf_counter()
         s = ops.rans_encode(sym, idx, cdf, length, offset)
-        coder_stats["encode_s"] += time.perf_counter() - t0
-        coder_stats["symbols"] += sym.size
+        _stat("encode_s", time.perf_counter() - t0)
+        _stat("symbols", sym.size)
         return s
 
     def decompress(self, strings, size):
@@ -385,6 +420,7 @@ class EntropyBottleneck(EntropyModel):
 class GaussianConditional(EntropyModel):
     """compressai.entropy_models.GaussianConditional (SURVEY.md Appendix B2;
     model/entropy_models.py:270,330,371-372,407-408)."""
+    _resizable_buffers = EntropyModel._resizable_buffers + ("scale_table",)
 
     def __init__(self, scale_table, *args, scale_bound=0.11, tail_mass=1e-9, **kwargs):
         super().__init__(*args, **kwargs)
@@ -500,6 +536,46 @@ class GaussianConditional(EntropyModel):
 
     def decompress_fused(self, string, params, rows, n, c):
         return drive(self.decompress_fused_gen(string, params, rows, n, c))
+
+
+class NonNegativeParametrizer(nn.Module):
+    """compressai.ops.parametrizers.NonNegativeParametrizer: x -> max(x, bound)^2 - pedestal."""
+
+    def __init__(self, minimum=0.0, reparam_offset=2 ** -18):
+        super().__init__()
+        pedestal = float(reparam_offset) ** 2
+        self.register_buffer("pedestal", torch.Tensor([pedestal]))
+        self.lower_bound = LowerBound((float(minimum) + pedestal) ** 0.5)
+
+    def init(self, x):
+        return torch.sqrt(torch.max(x + self.pedestal, self.pedestal))
+
+    def forward(self, x):
+        out = self.lower_bound(x)
+        return out ** 2 - self.pedestal
+
+
+class GDN(nn.Module):
+    """compressai.layers.GDN (model/blocks.py:258-260 subclasses it as MinkowskiGDN; ScaledBlock constructs
+    one, :27, and nothing on the codec path calls it): parameters ``beta`` [C], ``gamma`` [C, C] and the two
+    parametrizers, with CompressAI's dense forward y = x / sqrt(beta + gamma * x^2) over [B, C, ...]."""
+
+    def __init__(self, in_channels, inverse=False, beta_min=1e-6, gamma_init=0.1):
+        super().__init__()
+        self.inverse = bool(inverse)
+        self.beta_reparam = NonNegativeParametrizer(minimum=float(beta_min))
+        self.beta = nn.Parameter(self.beta_reparam.init(torch.ones(int(in_channels))))
+        self.gamma_reparam = NonNegativeParametrizer()
+        self.gamma = nn.Parameter(self.gamma_reparam.init(float(gamma_init) * torch.eye(int(in_channels))))
+
+    def forward(self, x):
+        C = x.shape[1]
+        beta = self.beta_reparam(self.beta)
+        gamma = self.gamma_reparam(self.gamma).reshape(C, C, *([1] * (x.dim() - 2)))
+        conv = {3: torch.nn.functional.conv1d, 4: torch.nn.functional.conv2d, 5: torch.nn.functional.conv3d}[x.dim()]
+        norm = conv(x ** 2, gamma, beta)
+        norm = torch.sqrt(norm) if self.inverse else torch.rsqrt(norm)
+        return x * norm
 
 
 class CompressionModel(nn.Module):

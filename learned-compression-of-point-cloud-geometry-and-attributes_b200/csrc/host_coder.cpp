@@ -296,12 +296,21 @@ int pcc_rans_decode_with_indexes(const uint8_t* enc, int64_t nbytes, const int32
         val = get_bits();
         nb += val;
       }
+      if (nb > 32 / kBypassBits) {  // a 32-bit value has at most 8 bypass nibbles: anything more is a corrupt stream
+        pcc::set_error("pcc_rans_decode_with_indexes: corrupt stream (bypass length %d at symbol %lld)", nb, (long long)i);
+        return PCC_ERR_INVALID_ARG;
+      }
       int32_t raw = 0;
-      for (int j = 0; j < nb; ++j) raw |= get_bits() << (j * kBypassBits);
+      for (int j = 0; j < nb; ++j) raw |= (int32_t)((uint32_t)get_bits() << (j * kBypassBits));
       value = raw >> 1;
       value = (raw & 1) ? (-value - 1) : (value + max_value);
     }
     symbols[i] = value + offsets[idx];
+    if (ptr > end) {  // a valid stream is consumed exactly; reading past it means it was truncated or tampered with
+      pcc::set_error("pcc_rans_decode_with_indexes: corrupt stream (exhausted at symbol %lld of %lld)", (long long)i,
+                     (long long)n);
+      return PCC_ERR_INVALID_ARG;
+    }
   }
   return PCC_OK;
 }

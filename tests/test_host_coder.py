@@ -74,3 +74,23 @@ def test_pmf_to_quantized_cdf_matches_oracle(pcc, oracle):
         assert a[0] == 0 and a[-1] == 65536 and (np.diff(a) > 0).all()
     with pytest.raises(pcc.PccError):
         pcc.ops.pmf_to_quantized_cdf(np.array([0.5, np.nan], np.float32))
+
+
+def test_rans_decoder_refuses_corrupt_streams(pcc, gc):
+    """a truncated / tampered stream is an error, not garbage symbols returned as PCC_OK."""
+    rng = np.random.default_rng(11)
+    n = 20000
+    idx = rng.integers(0, 64, size=n).astype(np.int32)
+    sym = np.rint(rng.standard_normal(n) * 30.0).astype(np.int32)
+    good = pcc.ops.rans_encode(sym, idx, gc.quantized_cdf, gc.cdf_length, gc.offset)
+    assert np.array_equal(pcc.ops.rans_decode(good, idx, gc.quantized_cdf, gc.cdf_length, gc.offset), sym)
+    with pytest.raises(pcc.PccError, match="corrupt stream"):          # cut in half: the decoder runs past the end
+        pcc.ops.rans_decode(good[:len(good) // 2 // 4 * 4], idx, gc.quantized_cdf, gc.cdf_length, gc.offset)
+    # garbage of the right length: either an over-long bypass run or an exhausted stream is hit, or (rarely) the
+    # noise decodes to in-range symbols — but never a crash, and never silently more words than the stream has
+    noise = rng.integers(0, 256, size=len(good), dtype=np.uint8).tobytes()
+    try:
+        out = pcc.ops.rans_decode(noise, idx, gc.quantized_cdf, gc.cdf_length, gc.offset)
+        assert out.shape == (n,)
+    except pcc.PccError as e:
+        assert "corrupt stream" in str(e)
