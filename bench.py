@@ -50,6 +50,8 @@ def parse_args():
                          "auto = threads when this rank's share of the host cores covers its launch and coder threads")
     ap.add_argument("--no-tf32-pass", action="store_true",
                     help="skip the secondary tensor-core (tf32) measurement added to the exact-mode line")
+    ap.add_argument("--no-scene-pass", action="store_true",
+                    help="N > 1: skip the secondary configs[4] record (one 5 M-point scene over the same ranks)")
     ap.add_argument("--scene", action="store_true",
                     help="configs[4]: ONE 12-bit ~5 M-point scene cut into x-slabs across the GPUs (halo exchange "
                          "per layer, strong scaling) instead of the frame-parallel headline workload")
@@ -334,6 +336,20 @@ def cpu_baseline(args, cfg_name, gpu_result=None):
 
 def run_scene(args, rank, world, local_rank):
     """BASELINE.json configs[4]: one large scene, spatially partitioned (pcc_b200.slab / .scene)."""
+    import torch
+    import pcc_b200
+    ops = pcc_b200.ops
+    dev = torch.device(f"cuda:{local_rank}")
+    torch.cuda.set_device(dev)
+    ops.set_default_mode(ops.MODE_TF32 if args.mode == "tf32" else ops.MODE_EXACT)
+    model, cfg = make_model(args.config, dev)
+    line = measure_scene(args, rank, world, local_rank, model, args.steps, args.warmup, args.verify)
+    if rank == 0:
+        print(json.dumps(line))
+
+
+def measure_scene(args, rank, world, local_rank, model, steps, warmup, verify):
+    """One scene, x-slabs over the ranks (every rank calls this) -> the JSON line (rank 0) or None."""
     import hashlib
     import torch
     import torch.distributed as dist
@@ -341,9 +357,6 @@ def run_scene(args, rank, world, local_rank):
     ops, scene, slab_m = pcc_b200.ops, pcc_b200.scene, pcc_b200.slab
 
     dev = torch.device(f"cuda:{local_rank}")
-    torch.cuda.set_device(dev)
-    ops.set_default_mode(ops.MODE_TF32 if args.mode == "tf32" else ops.MODE_EXACT)
-    model, cfg = make_model(args.config, dev)
     x = pcc_b200.synthetic.shell_frame(args.scene_radius, grid=args.scene_grid, seed=0)  # same on every rank
     Q = pcc_b200.synthetic.uniform_q_map(x, *args.q)
     n_scene = x.shape[0]
@@ -373,7 +386,7 @@ def run_scene(args, rank, world, local_rank):
     import gc
     res = {}
     for name, host_io in (("dev", False), ("e2e", True)):
-        for _ in range(args.warmup if name == "dev" else 1):
+        for _ in range(warmup if name == "dev" else 1):
             step(host_io)
         gc.collect()
         gc.disable()
@@ -385,7 +398,7 @@ def run_scene(args, rank, world, local_rank):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         t0 = time.perf_counter()
-        for _ in range(args.steps):
+        for _ in range(steps):
             s, c, out = step(host_io)
         e1.record()
         barrier()
@@ -403,7 +416,7 @@ def run_scene(args, rank, world, local_rank):
     else:
         per_rank = [own_pts.tolist()]
     verified = None
-    if args.verify:
+    if verify:
         s2, sh2, k2, c2 = scene.compress_scene(model, *resident, sl)
         full = scene.decompress_scene(model, c2, s2, sh2, k2, sl, gather=True)
         if rank == 0:
@@ -413,13 +426,13 @@ def run_scene(args, rank, world, local_rank):
             verified = bool(rs[0][0] == s2[0][0] and rs[1][0] == s2[1][0] and rsh == sh2 and rk == k2
                             and torch.equal(rc, c2) and torch.equal(ref.view(torch.int32), full.view(torch.int32)))
     if rank != 0:
-        return
+        return None
     h2d = (host[0].numel() + host[1].numel() + host[2].numel()) * 4
     d2h = out.numel() * 4
     line = {
-        "metric": "encode+decode points/sec, 5M-pt 12-bit scene (configs[4])", "value": n_scene * args.steps / t_dev,
-        "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "metric": "encode+decode points/sec, 5M-pt 12-bit scene (configs[4])", "value": n_scene * steps / t_dev,
+        "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
+        "ms_per_step": t_dev / steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32" if args.mode == "exact" else "tf32", "data": "synthetic",
         "config": {"workload": f"Ours.yaml random-init, encode+decode of ONE synthetic {args.scene_grid}^3-grid shell scene, "
                                f"radius {args.scene_radius:g} -> {n_scene} points, RGB, uniform q=({args.q[0]:g},{args.q[1]:g})",
@@ -427,14 +440,14 @@ def run_scene(args, rank, world, local_rank):
                    "neighbour send/recv per conv layer (NCCL), scene-wide top-k, latent gathered for the single rANS stream",
                    "points_in_out_per_rank": per_rank,
                    "l2": "working set exceeds the 126 MB L2; no flush", "includes_cpu_range_coder": True},
-        "e2e": {"value": n_scene * args.steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": t_e2e / args.steps * 1e3, "note": "per rank: its slab H2D from pinned memory, its decoded slab D2H"},
+        "e2e": {"value": n_scene * steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": t_e2e / steps * 1e3, "note": "per rank: its slab H2D from pinned memory, its decoded slab D2H"},
         "gpu_launches": res["dev"]["launches"], "clocks": res.get("clocks", {}),
         "string_sha1": hashlib.sha1(s[0][0] + s[1][0]).hexdigest(),
     }
     if verified is not None:
         line["verified_bit_exact_vs_one_gpu"] = verified
-    print(json.dumps(line))
+    return line
 
 
 def run_ours(args, rank, world, local_rank):
@@ -562,9 +575,47 @@ def run_ours(args, rank, world, local_rank):
         torch.cuda.synchronize()
         lat.append(round((time.perf_counter() - tw) * 1e3, 2))
     gpu_result = (s_, sh_, k_, c_.cpu().numpy(), out_.cpu().numpy())
+    # the interval the reference itself times (utils.py:448-464): compress(path=...) + decompress(path=...) through
+    # the latent-coordinate side channel and the container, one frame at a time, file on tmpfs
+    file_variant = None
+    if rank == 0:
+        fdir = "/dev/shm" if os.path.isdir("/dev/shm") else tempfile.gettempdir()
+        fpath = os.path.join(fdir, f"pcc_b200_bench_{os.getpid()}.bin")
+        try:
+            ft = []
+            for _ in range(3):
+                torch.cuda.synchronize()
+                tw = time.perf_counter()
+                model.compress(*dev_inputs[0], path=fpath)
+                tm = time.perf_counter()
+                fout = model.decompress(path=fpath)
+                torch.cuda.synchronize()
+                ft.append((round((tm - tw) * 1e3, 2), round((time.perf_counter() - tm) * 1e3, 2)))
+            fbytes = os.path.getsize(fpath)
+            from pcc_b200.bitstream import gpcc_encode
+            side = len(gpcc_encode(c_))
+            file_variant = {"compress_ms": [a for a, _ in ft], "decompress_ms": [b for _, b in ft],
+                            "points_per_s": dev_inputs[0][0].shape[0] / (min(a + b for a, b in ft) * 1e-3),
+                            "file_bytes": fbytes, "bpp": fbytes * 8.0 / dev_inputs[0][0].shape[0],
+                            "side_channel_bytes": side, "side_channel_bytes_per_latent_voxel": side / c_.shape[0],
+                            "decoded_equals_in_memory": bool(torch.equal(fout, out_)),
+                            "note": "one frame at a time (no pipelining), ColorModel.compress(x, Q, path) + "
+                                    ".decompress(path): own octree side channel instead of the reference's tmc3 "
+                                    "subprocess, container of model/model.py:214-315; file on tmpfs"}
+        finally:
+            if os.path.exists(fpath):
+                os.unlink(fpath)
     gc.enable()
     pipe.close()
     (t_dev, t_e2e), npts_all = pcc_b200.frames.reduce_throughput([t_dev, t_e2e], npts, dev)
+    # configs[4] as a secondary record of every multi-GPU run: ONE 12-bit ~5 M-point scene cut into x-slabs over the
+    # same ranks (halo exchange per conv layer over NCCL, strong scaling), verified against one GPU
+    scene_line = None
+    if world > 1 and not args.no_scene_pass:
+        try:
+            scene_line = measure_scene(args, rank, world, local_rank, model, steps=2, warmup=1, verify=True)
+        except Exception as e:  # the headline line must survive a failure of the secondary measurement
+            scene_line = {"error": f"{type(e).__name__}: {e}"[:300]}
     if rank != 0:
         return
 
@@ -614,6 +665,14 @@ def run_ours(args, rank, world, local_rank):
         line["cpu_baseline"] = base
     if verified is not None:
         line["verified_bit_exact_vs_oracle"] = verified
+    if file_variant is not None:
+        line["file_variant"] = file_variant
+    if scene_line is not None:
+        keep = ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "scaling", "e2e", "gpu_launches",
+                "verified_bit_exact_vs_one_gpu", "string_sha1", "error")
+        line["scene"] = {k: scene_line[k] for k in keep if k in scene_line}
+        if "config" in scene_line:
+            line["scene"]["config"] = {k: scene_line["config"][k] for k in ("workload", "parallelism", "points_in_out_per_rank")}
     print(json.dumps(line))
 
 
