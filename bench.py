@@ -622,6 +622,20 @@ def run_ours(args, rank, world, local_rank):
     roof = None
     if not args.no_roofline:
         roof, _ = roofline_pass(model, *dev_inputs[0], peaks, clocks, args.dump_layers)
+        if roof is not None and world == 1:
+            # every non-dense kernel class of the path (hashing, kernel map, stride / expand / sort, top-k,
+            # quantise + index, gathers, small-channel convolutions) on this frame's maps: algorithmic bytes
+            # (SURVEY.md 8(d) per-unit figures) / CUDA-event time, as a fraction of the measured HBM copy rate
+            try:
+                from tools.class_bench import measure_classes
+                roof["classes"] = [
+                    {k: (round(v, 4) if isinstance(v, float) else v) for k, v in c.items() if k != "kernels"}
+                    for c in measure_classes(device=str(dev), radius=args.radius, grid=args.grid, reps=3,
+                                             hbm_gbs=peaks.get("hbm_gbs"))]
+                roof["classes_peak"] = {"hbm_gbs": peaks.get("hbm_gbs", 6650.0),
+                                        "source": "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback"}
+            except Exception as e:
+                roof["classes_error"] = f"{type(e).__name__}: {e}"[:200]
     tf32 = None
     if world == 1 and args.mode == "exact" and not args.no_tf32_pass:
         tf32 = tf32_pass(args, model, dev, dev_inputs[0], B, peaks, clocks)

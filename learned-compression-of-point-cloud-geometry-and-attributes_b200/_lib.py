@@ -7,7 +7,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpcc_b200.so")
+# PCC_B200_LIB: another build of the same library (kernel A/B experiments); default = the in-tree build
+LIB_PATH = os.environ.get("PCC_B200_LIB") or os.path.join(_HERE, "libpcc_b200.so")
 
 P = ctypes.c_void_p
 I64 = ctypes.c_int64

@@ -20,7 +20,10 @@ constexpr int CE_TM = PCC_TILE_M;  // 128 output rows
 constexpr int CE_TK = 32;          // input channels per stage
 constexpr int CE_THREADS = 256;    // 16 x 16
 constexpr int CE_STAGES = 3;
-constexpr int CE_APITCH = CE_TK + 4;  // floats; keeps 16 B alignment, rows r and r+1 4 banks apart
+constexpr int CE_APITCH = CE_TK + 4;
+#ifndef CE_KV_UNROLL
+#define CE_KV_UNROLL 8  // 4-channel steps of a stage unrolled in the FMA loop (8 = the whole 32-channel stage)
+#endif  // floats; keeps 16 B alignment, rows r and r+1 4 banks apart
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem, int src_bytes) {
   const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
@@ -102,11 +105,70 @@ __device__ __forceinline__ void ffma2(unsigned long long& d, unsigned long long 
   asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
 }
 
+
+// One pipeline stage of the register-tile loop: TK input channels of the staged rows (a: [CE_TM][TK + 4]) times the
+// staged weight slice (b: [TK][TN]) into the thread's 8 x CN accumulators, ascending ci.  Shared by the cp.async
+// kernel and the bulk-copy kernel below, so both issue the same FMA chain.
+template <int TN, int TK, bool PK>
+__device__ __forceinline__ void exact_stage_fma(const float* __restrict__ sa, const float* __restrict__ sb, int rbase,
+                                                int cbase, float (&acc)[8][TN / 16],
+                                                unsigned long long (&acc2)[8][PK ? TN / 32 : 1]) {
+  constexpr int CN = TN / 16;
+  constexpr int AV = 4;
+  constexpr int CP = PK ? CN / 2 : 1;
+  constexpr int AP = TK + 4;
+  constexpr int KVU = CE_KV_UNROLL;
+#pragma unroll KVU
+  for (int kv = 0; kv < TK / AV; ++kv) {
+    float a[8][AV];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float4 v = *reinterpret_cast<const float4*>(sa + (rbase + 4 * i) * AP + kv * AV);
+      a[i][0] = v.x; a[i][1] = v.y; a[i][2] = v.z; a[i][3] = v.w;
+    }
+#pragma unroll
+    for (int e = 0; e < AV; ++e) {
+      float b[CN];
+      const float* brow = sb + (kv * AV + e) * TN;
+      if (CN == 8) {
+        const float4 b0 = *reinterpret_cast<const float4*>(brow + cbase);
+        const float4 b1 = *reinterpret_cast<const float4*>(brow + cbase + 32);
+        b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w;
+        b[4 % CN] = b1.x; b[5 % CN] = b1.y; b[6 % CN] = b1.z; b[7 % CN] = b1.w;
+      } else if (CN == 4) {
+        const float4 b0 = *reinterpret_cast<const float4*>(brow + cbase);
+        b[0] = b0.x; b[1 % CN] = b0.y; b[2 % CN] = b0.z; b[3 % CN] = b0.w;
+      } else if (CN == 2) {
+        const float2 b0 = *reinterpret_cast<const float2*>(brow + cbase);
+        b[0] = b0.x; b[1 % CN] = b0.y;
+      } else {
+        b[0] = brow[cbase];
+      }
+      if (PK) {
+        unsigned long long bp[CP];
+#pragma unroll
+        for (int c = 0; c < CP; ++c) bp[c] = pack2(b[(2 * c) % CN], b[(2 * c + 1) % CN]);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const unsigned long long aa = pack2(a[i][e], a[i][e]);
+#pragma unroll
+          for (int c = 0; c < CP; ++c) ffma2(acc2[i][c], aa, bp[c]);
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+#pragma unroll
+          for (int c = 0; c < CN; ++c) acc[i][c] = __fmaf_rn(a[i][e], b[c], acc[i][c]);
+        }
+      }
+    }
+  }
+}
+
 template <int TN, bool VEC, int F2, int TK = CE_TK>
 __global__ void __launch_bounds__(CE_THREADS, 2)
 conv_exact_kernel(const ConvParams p) {
   constexpr int CN = TN / 16;  // output channels per thread
-  constexpr int AV = 4;        // floats of a gathered row per shared-memory load (LDS.128)
   constexpr bool PK = (F2 != 0) && (CN % 2 == 0);
   constexpr int CP = PK ? CN / 2 : 1;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -256,57 +318,7 @@ conv_exact_kernel(const ConvParams p) {
     cp_async_commit();
 
     const int st = s % CE_STAGES;
-#pragma unroll
-    for (int kv = 0; kv < TK / AV; ++kv) {
-      float a[8][AV];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float* ap = &sm.a[st][rbase + 4 * i][kv * AV];
-        if (AV == 4) {
-          const float4 v = *reinterpret_cast<const float4*>(ap);
-          a[i][0] = v.x; a[i][1] = v.y; a[i][2 % AV] = v.z; a[i][3 % AV] = v.w;
-        } else {
-          const float2 v = *reinterpret_cast<const float2*>(ap);
-          a[i][0] = v.x; a[i][1] = v.y;
-        }
-      }
-#pragma unroll
-      for (int e = 0; e < AV; ++e) {
-        float b[CN];
-        const float* brow = &sm.b[st][kv * AV + e][0];
-        if (CN == 8) {
-          const float4 b0 = *reinterpret_cast<const float4*>(brow + cbase);
-          const float4 b1 = *reinterpret_cast<const float4*>(brow + cbase + 32);
-          b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w;
-          b[4 % CN] = b1.x; b[5 % CN] = b1.y; b[6 % CN] = b1.z; b[7 % CN] = b1.w;
-        } else if (CN == 4) {
-          const float4 b0 = *reinterpret_cast<const float4*>(brow + cbase);
-          b[0] = b0.x; b[1 % CN] = b0.y; b[2 % CN] = b0.z; b[3 % CN] = b0.w;
-        } else if (CN == 2) {
-          const float2 b0 = *reinterpret_cast<const float2*>(brow + cbase);
-          b[0] = b0.x; b[1 % CN] = b0.y;
-        } else {
-          b[0] = brow[cbase];
-        }
-        if (PK) {
-          unsigned long long bp[CP];
-#pragma unroll
-          for (int c = 0; c < CP; ++c) bp[c] = pack2(b[(2 * c) % CN], b[(2 * c + 1) % CN]);
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const unsigned long long aa = pack2(a[i][e], a[i][e]);
-#pragma unroll
-            for (int c = 0; c < CP; ++c) ffma2(acc2[i][c], aa, bp[c]);
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-#pragma unroll
-            for (int c = 0; c < CN; ++c) acc[i][c] = __fmaf_rn(a[i][e], b[c], acc[i][c]);
-          }
-        }
-      }
-    }
+    exact_stage_fma<TN, TK, PK>(&sm.a[st][0][0], &sm.b[st][0][0], rbase, cbase, acc, acc2);
   }
   cp_async_wait<0>();
   if (PK) {
@@ -335,6 +347,204 @@ conv_exact_kernel(const ConvParams p) {
         p.out[o * p.out_stride + col] = acc[i][c];
     }
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Bulk-copy producer (cin % 32 == 0, 16-byte aligned operands, packed FMA): same tile, same register mapping and
+// the same exact_stage_fma as conv_exact_kernel, but the producer side of a stage — 8 cp.async per thread with
+// their address arithmetic, 1024 + 1024 lane-instructions per CTA — becomes ONE cp.async.bulk instruction per warp:
+// lanes 0-15 of warp w copy the 128-byte chunks of tile rows 16 w .. 16 w + 15 (a missing neighbour copies the
+// zero row), lanes 16-19 the weight rows 4 w .. 4 w + 3 of the stage.  The copies complete on the stage's
+// mbarrier (complete_tx), which takes the place of cp.async.wait_group; the one __syncthreads per stage that
+// frees the slot being refilled stays.  The FMA order is untouched, so results are bit-identical.
+__device__ __align__(128) float g_zero_row[CE_TK];  // 128 zero bytes: the source of a missing neighbour's chunk
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n}\n" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n .reg .pred p;\n"
+      "WAIT_%=:\n"
+      " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, 0x989680;\n"
+      " @!p bra WAIT_%=;\n}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+template <int TN>
+struct BulkSmem {
+  float a[CE_STAGES][CE_TM][CE_TK + 4];
+  float b[CE_STAGES][CE_TK][TN];
+  uint64_t full[CE_STAGES];
+};
+
+template <int TN>
+__global__ void __launch_bounds__(CE_THREADS, 2)
+conv_exact_bulk_kernel(const ConvParams p) {
+  constexpr int TK = CE_TK;
+  constexpr int CN = TN / 16;
+  constexpr int CP = CN / 2;
+  static_assert(CN % 2 == 0, "packed accumulators");
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  BulkSmem<TN>& sm = *reinterpret_cast<BulkSmem<TN>*>(smem_raw);
+
+  const int tid = threadIdx.x;
+  const int lane = tid & 31, wid = tid >> 5;
+  const int tx = lane & 7, ty = lane >> 3;
+  const int rbase = (wid >> 1) * 32 + ty;
+  const int cbase = (wid & 1) * (TN / 2) + tx * (CN == 8 ? 4 : CN);
+  const unsigned tile = p.tile_order ? (unsigned)__ldg(p.tile_order + blockIdx.x) : blockIdx.x;
+  const int64_t tile_base = (int64_t)tile * CE_TM;
+  const int co_base = blockIdx.y * TN;
+  const int nchunks = p.cin / TK;
+  const uint32_t mask = p.tapmask ? (p.tapmask[tile] & p.kbits) : p.kbits;
+  const int nsteps = __popc(mask) * nchunks;
+  if (nsteps == 0 && !p.first && !p.last) return;  // CTA-uniform
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < CE_STAGES; ++s) mbar_init(&sm.full[s], CE_THREADS / 32);  // one expect_tx arrival per warp
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  __syncthreads();
+
+  float acc[8][CN];
+  unsigned long long acc2[8][CP];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+#pragma unroll
+    for (int c = 0; c < CN; ++c) acc[i][c] = 0.0f;
+#pragma unroll
+    for (int c = 0; c < CP; ++c) acc2[i][c] = 0ull;
+  }
+  if (!p.first) {  // continue the FMA chains from the previous group's partial sums
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int64_t t = tile_base + rbase + 4 * i;
+      if (t >= p.n_out) continue;
+      const int64_t o = p.order ? (int64_t)__ldg(p.order + t) : t;
+#pragma unroll
+      for (int c = 0; c < CN; ++c) {
+        const int col = co_base + cbase + ((CN == 8) ? ((c >> 2) * 32 + (c & 3)) : c);
+        if (col < p.cout) acc[i][c] = p.out[o * p.out_stride + col];
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int c = 0; c < CP; ++c) acc2[i][c] = pack2(acc[i][2 * c], acc[i][2 * c + 1]);
+  }
+
+  // producer cursor: lanes 0-15 hold the kernel-map entry of tile row 16 wid + lane for the current offset (idx)
+  // and for the next active one (nidx)
+  uint32_t pmask = mask;
+  int pk = pmask ? (__ffs(pmask) - 1) : 0;
+  int pchunk = 0;
+  const int arow = wid * 16 + (lane & 15);
+  auto load_idx = [&](int k) -> int {
+    const int64_t t = tile_base + arow;
+    return (lane < 16 && t < p.n_out) ? __ldg(p.nbr + (int64_t)k * p.nbr_stride + t) : -1;
+  };
+  int idx = load_idx(pk), nidx = -1;
+  {
+    const uint32_t rest = pmask & (pmask - 1);
+    if (rest) nidx = load_idx(__ffs(rest) - 1);
+  }
+  const int ncols = (p.cout - co_base) < TN ? (p.cout - co_base) : TN;  // valid columns of this CTA's weight slice
+  const uint32_t b_row_bytes = (uint32_t)ncols * 4u;
+  const uint32_t warp_tx = 16u * (TK * 4u) + 4u * b_row_bytes;
+
+  auto issue = [&](int stage) {
+    const int ci0 = pchunk * TK;
+    if (lane == 0) mbar_expect_tx(&sm.full[stage], warp_tx);
+    __syncwarp();
+    if (lane < 16) {
+      const float* src = idx >= 0 ? p.in + (int64_t)idx * p.cin + ci0 : g_zero_row;
+      bulk_g2s(&sm.a[stage][arow][0], src, TK * 4u, &sm.full[stage]);
+    } else if (lane < 20) {
+      const int kk = wid * 4 + (lane - 16);
+      const float* src = p.weight + ((int64_t)pk * p.cin + ci0 + kk) * p.cout + co_base;
+      bulk_g2s(&sm.b[stage][kk][0], src, b_row_bytes, &sm.full[stage]);
+    }
+    if (++pchunk == nchunks) {
+      pchunk = 0;
+      pmask &= pmask - 1;
+      pk = pmask ? (__ffs(pmask) - 1) : 0;
+      idx = nidx;
+      const uint32_t rest = pmask & (pmask - 1);
+      if (rest) nidx = load_idx(__ffs(rest) - 1);
+    }
+  };
+
+#pragma unroll
+  for (int s = 0; s < CE_STAGES - 1; ++s)
+    if (s < nsteps) issue(s);
+
+  for (int s = 0; s < nsteps; ++s) {
+    const int st = s % CE_STAGES;
+    mbar_wait(&sm.full[st], (uint32_t)((s / CE_STAGES) & 1));  // this stage's copies have landed
+    __syncthreads();  // every warp is done with step s - 1: its slot may be refilled
+    if (s + CE_STAGES - 1 < nsteps) issue((s + CE_STAGES - 1) % CE_STAGES);
+    exact_stage_fma<TN, TK, true>(&sm.a[st][0][0], &sm.b[st][0][0], rbase, cbase, acc, acc2);
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int c = 0; c < CP; ++c) unpack2(acc2[i][c], acc[i][2 * c], acc[i][2 * c + 1]);
+
+  // ---- epilogue: bias -> activation -> FiLM -> residual -> store
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int64_t t = tile_base + rbase + 4 * i;  // tile row -> output row
+    if (t >= p.n_out) continue;
+    const int64_t o = p.order ? (int64_t)__ldg(p.order + t) : t;
+    int64_t frow = o, rrow = o;
+    if (p.film_c && p.film_rows) frow = __ldg(p.film_rows + o);
+    if (p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
+#pragma unroll
+    for (int c = 0; c < CN; ++c) {
+      const int col = co_base + cbase + ((CN == 8) ? ((c >> 2) * 32 + (c & 3)) : c);
+      if (col >= p.cout) continue;
+      if (p.last)
+        conv_epilogue(p, o, frow, rrow, col, acc[i][c]);
+      else
+        p.out[o * p.out_stride + col] = acc[i][c];
+    }
+  }
+}
+
+template <int TN>
+static int launch_exact_bulk(const ConvParams& p, cudaStream_t st) {
+  const size_t smem = sizeof(BulkSmem<TN>);
+  dim3 grid((unsigned)ceil_div(p.n_out, CE_TM), (unsigned)ceil_div(p.cout, TN));
+  static const cudaError_t attr = cudaFuncSetAttribute(conv_exact_bulk_kernel<TN>,
+                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  PCC_CHECK_CUDA(attr);
+  conv_exact_bulk_kernel<TN><<<grid, CE_THREADS, smem, st>>>(p);
+  PCC_CHECK_LAUNCH("conv_exact_bulk_kernel");
+  return PCC_OK;
+}
+
+// PCC_EXACT_BULK=0 keeps the cp.async producer everywhere (for A/B timing)
+static int exact_bulk() {
+  static int v = [] {
+    const char* e = getenv("PCC_EXACT_BULK");
+    return e ? atoi(e) : 1;
+  }();
+  return v;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -503,6 +713,14 @@ static int launch_exact(const ConvParams& p, cudaStream_t st) {
                    ((reinterpret_cast<uintptr_t>(p.in) & 15) == 0) &&
                    ((reinterpret_cast<uintptr_t>(p.weight) & 15) == 0);
   const int f2 = exact_f2();
+  // measured on the 799,458-point frame (profiles/r02_*): the bulk-copy producer is 2 % faster on the 128-wide
+  // tiles (1.19 M x 128 -> 128: 14.44 -> 14.18 ms) and 7 % slower on the 64-wide ones (twice the copies per FMA), so
+  // only the 128-wide kernel uses it; PCC_EXACT_BULK=2 forces it for 64- and 32-wide tiles too
+  if constexpr (TN >= 32) {
+    const int bulk = exact_bulk();
+    if (vec && f2 != 0 && p.cin % CE_TK == 0 && (bulk >= 2 || (bulk == 1 && TN == 128)))
+      return launch_exact_bulk<TN>(p, st);
+  }
   if (p.cin <= 4 && f2 != 0)  // thin input (the Q branch, the xyz/rgb input layer): 4-channel stages
     return vec ? launch_exact_v<TN, true, 1, 4>(p, st) : launch_exact_v<TN, false, 1, 4>(p, st);
   if (f2 != 0) return vec ? launch_exact_v<TN, true, 1>(p, st) : launch_exact_v<TN, false, 1>(p, st);

@@ -85,11 +85,11 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "{\n"
       " .reg .pred p;\n"
       "WAIT_LOOP:\n"
-      " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"  // suspend until the phase flips (time cap)
       " @p bra DONE;\n"
       " bra WAIT_LOOP;\n"
       "DONE:\n"
-      "}\n" ::"r"(bar), "r"(parity) : "memory");
+      "}\n" ::"r"(bar), "r"(parity), "r"(0x989680u) : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }

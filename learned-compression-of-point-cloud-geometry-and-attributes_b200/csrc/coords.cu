@@ -269,14 +269,25 @@ kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict_
   if (threadIdx.x == 0 && tapmask) tapmask[blockIdx.x] = smask;
 }
 
-// sort key of row j for one offset group: (j / seg_rows, the group's bits of the row's neighbour mask)
+// sort key of row j for one offset group: (j / seg_rows, the group's bits of the row's neighbour mask).
+// The sort only has to bring rows with EQUAL masks together (which masks end up next to each other does not
+// matter), and a map has a few hundred distinct masks, so a mask of more than GROUP_HASH_BITS bits is replaced by a
+// 16-bit multiplicative hash of it: two radix passes instead of four for a 27-bit mask.  Two masks that collide
+// (about one pair per map) share their tiles, which costs those tiles some skipped-offset efficiency, never a result.
+constexpr int GROUP_HASH_BITS = 16;
+__host__ __device__ __forceinline__ int group_key_bits(int mask_bits) {
+  return mask_bits > GROUP_HASH_BITS ? GROUP_HASH_BITS : mask_bits;
+}
+
 template <typename KeyT>
 __global__ void group_key_kernel(const uint32_t* __restrict__ row_masks, int64_t n, int k_lo, int k_hi, int seg_shift,
                                  KeyT* __restrict__ keys, int32_t* __restrict__ iota) {
   const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n) return;
-  const uint32_t sub = (row_masks[j] >> k_lo) & (uint32_t)((1ull << (k_hi - k_lo)) - 1ull);
-  keys[j] = (KeyT)(((uint64_t)(j >> seg_shift) << (k_hi - k_lo)) | sub);
+  const int mb = k_hi - k_lo;
+  uint32_t sub = (row_masks[j] >> k_lo) & (uint32_t)((1ull << mb) - 1ull);
+  if (mb > GROUP_HASH_BITS) sub = (sub * 0x9E3779B1u) >> (32 - GROUP_HASH_BITS);
+  keys[j] = (KeyT)(((uint64_t)(j >> seg_shift) << group_key_bits(mb)) | sub);
   iota[j] = (int32_t)j;
 }
 
@@ -298,7 +309,7 @@ static size_t cub_sort_keys_bytes(int64_t n) {
 static int sort_rows_by_group_key(const uint32_t* row_masks, int64_t n, int k_lo, int k_hi, int seg_shift, int seg_bits,
                                   void* k_in, void* k_out, int32_t* iota, int32_t* order_out, void* cub_ws,
                                   size_t cub_bytes, cudaStream_t st) {
-  const int bits = (k_hi - k_lo) + seg_bits;
+  const int bits = group_key_bits(k_hi - k_lo) + seg_bits;
   const unsigned grid = (unsigned)ceil_div(n, 256);
   if (bits <= 32) {
     size_t need = 0;

@@ -133,7 +133,10 @@ def _model(pcc, cfg):
 
 @pytest.mark.parametrize("config_name,q", [("OURS_CONFIG", (0.5, 0.5)), ("OURS_CONFIG", (0.0, 0.0)),
                                            ("OURS_CONFIG", (1.0, 1.0)), ("OURS_CONFIG", (0.0, 1.0)),
-                                           ("OURS_CONFIG", (1.0, 0.0)), ("ABLATION_CONFIG", (0.5, 0.5))])
+                                           ("OURS_CONFIG", (1.0, 0.0)), ("ABLATION_CONFIG", (0.5, 0.5)),
+                                           # the rest of configs[1]'s sweep {0, 0.5, 1}^2
+                                           ("OURS_CONFIG", (0.0, 0.5)), ("OURS_CONFIG", (0.5, 0.0)),
+                                           ("OURS_CONFIG", (0.5, 1.0)), ("OURS_CONFIG", (1.0, 0.5))])
 def test_codec_round_trip_full_size(pcc, frame, config_name, q):
     model = _model(pcc, getattr(pcc, config_name))
     x = frame
