@@ -225,7 +225,7 @@ kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict_
                   uint64_t cap_mask, const uint64_t* __restrict__ out_keys, int64_t n_out, int step,
                   int in_align, const int32_t* __restrict__ order, int32_t* __restrict__ nbr,
                   int64_t nbr_stride, uint32_t* __restrict__ tapmask, uint32_t* __restrict__ row_masks,
-                  int k_lo, int k_hi) {
+                  int k_lo, int k_hi, int32_t* __restrict__ found) {
   constexpr int K = KS * KS * KS;
   constexpr int LO = (KS == 3) ? -1 : 0;
   __shared__ uint32_t smask;
@@ -256,6 +256,7 @@ kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict_
         (((qx | qy | qz) & amask) == 0))
       r = hash_find(tkeys, tvals, cap_mask, pack_key(b, qx, qy, qz));
     if (!MASK_ONLY && live) nbr[(int64_t)k * nbr_stride + j] = r;
+    if (MASK_ONLY && found && live) found[(int64_t)k * n_out + j] = r;  // [K][n_out], output-row order
     if (r >= 0) mine |= 1u << k;
   }
   if (MASK_ONLY) {
@@ -269,25 +270,51 @@ kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict_
   if (threadIdx.x == 0 && tapmask) tapmask[blockIdx.x] = smask;
 }
 
-// sort key of row j for one offset group: (j / seg_rows, the group's bits of the row's neighbour mask).
-// The sort only has to bring rows with EQUAL masks together (which masks end up next to each other does not
-// matter), and a map has a few hundred distinct masks, so a mask of more than GROUP_HASH_BITS bits is replaced by a
-// 16-bit multiplicative hash of it: two radix passes instead of four for a 27-bit mask.  Two masks that collide
-// (about one pair per map) share their tiles, which costs those tiles some skipped-offset efficiency, never a result.
-constexpr int GROUP_HASH_BITS = 16;
-__host__ __device__ __forceinline__ int group_key_bits(int mask_bits) {
-  return mask_bits > GROUP_HASH_BITS ? GROUP_HASH_BITS : mask_bits;
+// Write pass after a mask pass that kept its probe results (found: [K][n_out] in output-row order): tile row j of
+// the group takes the entries of output row order[j] — a permuted copy, no second walk through the hash table —
+// and the warp votes the tile's tap mask as kernel_map_kernel does.
+template <int KS>
+__global__ void __launch_bounds__(PCC_TILE_M)
+kernel_map_permute_kernel(const int32_t* __restrict__ found, int64_t n_out, const int32_t* __restrict__ order,
+                          int32_t* __restrict__ nbr, int64_t nbr_stride, uint32_t* __restrict__ tapmask, int k_lo,
+                          int k_hi) {
+  constexpr int K = KS * KS * KS;
+  __shared__ uint32_t smask;
+  if (threadIdx.x == 0) smask = 0;
+  __syncthreads();
+  const int64_t j = (int64_t)blockIdx.x * PCC_TILE_M + threadIdx.x;
+  const bool live = j < n_out;
+  const int64_t o = live ? (int64_t)__ldg(order + j) : 0;
+  uint32_t mine = 0;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    if (k < k_lo || k >= k_hi) continue;
+    if (live) {
+      const int32_t r = __ldg(found + (int64_t)k * n_out + o);
+      nbr[(int64_t)k * nbr_stride + j] = r;
+      if (r >= 0) mine |= 1u << k;
+    }
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) mine |= __shfl_xor_sync(0xffffffffu, mine, s);
+  if ((threadIdx.x & 31) == 0 && mine) atomicOr(&smask, mine);
+  __syncthreads();
+  if (threadIdx.x == 0 && tapmask) tapmask[blockIdx.x] = smask;
 }
 
+// sort key of row j for one offset group: (j / seg_rows, the group's bits of the row's neighbour mask).
+// The sort is by mask VALUE on purpose.  A surface map has thousands of distinct masks, many with fewer rows than a
+// tile, so most tiles hold several masks; in value order neighbouring masks share their high offsets and the union
+// a tile computes stays small.  Replacing the mask by a 16-bit hash (two radix passes instead of four) was tried in
+// round 2: tiles then mix unrelated masks, the useful-MAC share of the 799,458-voxel map fell below the 0.72
+// threshold and the map was cut into three offset groups (tests/test_gpu_fullsize.py caught it).
 template <typename KeyT>
 __global__ void group_key_kernel(const uint32_t* __restrict__ row_masks, int64_t n, int k_lo, int k_hi, int seg_shift,
                                  KeyT* __restrict__ keys, int32_t* __restrict__ iota) {
   const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n) return;
-  const int mb = k_hi - k_lo;
-  uint32_t sub = (row_masks[j] >> k_lo) & (uint32_t)((1ull << mb) - 1ull);
-  if (mb > GROUP_HASH_BITS) sub = (sub * 0x9E3779B1u) >> (32 - GROUP_HASH_BITS);
-  keys[j] = (KeyT)(((uint64_t)(j >> seg_shift) << group_key_bits(mb)) | sub);
+  const uint32_t sub = (row_masks[j] >> k_lo) & (uint32_t)((1ull << (k_hi - k_lo)) - 1ull);
+  keys[j] = (KeyT)(((uint64_t)(j >> seg_shift) << (k_hi - k_lo)) | sub);
   iota[j] = (int32_t)j;
 }
 
@@ -309,7 +336,7 @@ static size_t cub_sort_keys_bytes(int64_t n) {
 static int sort_rows_by_group_key(const uint32_t* row_masks, int64_t n, int k_lo, int k_hi, int seg_shift, int seg_bits,
                                   void* k_in, void* k_out, int32_t* iota, int32_t* order_out, void* cub_ws,
                                   size_t cub_bytes, cudaStream_t st) {
-  const int bits = group_key_bits(k_hi - k_lo) + seg_bits;
+  const int bits = (k_hi - k_lo) + seg_bits;
   const unsigned grid = (unsigned)ceil_div(n, 256);
   if (bits <= 32) {
     size_t need = 0;
@@ -546,9 +573,9 @@ int pcc_coords_expand(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, 
 
 size_t pcc_kernel_map_ws_bytes(int64_t n_out) {
   if (n_out <= 0) return 256;
-  // sort keys in | sort keys out | iota | row masks | cub | two counters
+  // sort keys in | sort keys out | iota | row masks | cub | two counters | the mask pass's probe results [27][n_out]
   return align_up((size_t)n_out * 8, 256) * 2 + align_up((size_t)n_out * 4, 256) * 2 +
-         align_up(cub_sort_pairs_bytes(n_out), 256) + 256;
+         align_up(cub_sort_pairs_bytes(n_out), 256) + 256 + align_up((size_t)n_out * 27 * 4, 256);
 }
 
 }  // extern "C"
@@ -621,7 +648,7 @@ static int kernel_map_launch(const uint64_t* tkeys, const int32_t* tvals, uint64
   const unsigned grid = (unsigned)ceil_div(n_out, PCC_TILE_M);
   if (!order) {
     kernel_map_kernel<KS, false><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align,
-                                                             nullptr, nbr, nbr_stride, tapmask, nullptr, 0, K);
+                                                             nullptr, nbr, nbr_stride, tapmask, nullptr, 0, K, nullptr);
     PCC_CHECK_LAUNCH("kernel_map_kernel");
     if (tile_order && tapmask) {
       tile_rank_kernel<<<1, 1024, 0, st>>>(tapmask, (int)grid, tile_order);
@@ -640,8 +667,10 @@ static int kernel_map_launch(const uint64_t* tkeys, const int32_t* tvals, uint64
   uint32_t* row_masks = reinterpret_cast<uint32_t*>(w + 2 * align_up((size_t)n_out * 8, 256) + align_up((size_t)n_out * 4, 256));
   void* cub_ws = w + 2 * align_up((size_t)n_out * 8, 256) + 2 * align_up((size_t)n_out * 4, 256);
   size_t cub_bytes = align_up(cub_sort_pairs_bytes(n_out), 256);
+  // every neighbour is probed ONCE: the mask pass keeps what it found, the write passes permute it
+  int32_t* found = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(cub_ws) + cub_bytes + 256);
   kernel_map_kernel<KS, true><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align,
-                                                          nullptr, nullptr, 0, nullptr, row_masks, 0, K);
+                                                          nullptr, nullptr, 0, nullptr, row_masks, 0, K, found);
   PCC_CHECK_LAUNCH("kernel_map_kernel<mask>");
   bool have_order0 = false;
   if (n_groups == 0) {
@@ -673,11 +702,9 @@ static int kernel_map_launch(const uint64_t* tkeys, const int32_t* tvals, uint64
                                             order_g, cub_ws, cub_bytes, st);
       if (rc) return rc;
     }
-    kernel_map_kernel<KS, false><<<grid, PCC_TILE_M, 0, st>>>(tkeys, tvals, cm, out_keys, n_out, step, in_align,
-                                                             order_g, nbr, nbr_stride,
-                                                             tapmask ? tapmask + (int64_t)g * grid : nullptr, row_masks,
-                                                             k_lo, k_hi);
-    PCC_CHECK_LAUNCH("kernel_map_kernel");
+    kernel_map_permute_kernel<KS><<<grid, PCC_TILE_M, 0, st>>>(found, n_out, order_g, nbr, nbr_stride,
+                                                              tapmask ? tapmask + (int64_t)g * grid : nullptr, k_lo, k_hi);
+    PCC_CHECK_LAUNCH("kernel_map_permute_kernel");
     if (tile_order && tapmask) {
       tile_rank_kernel<<<1, 1024, 0, st>>>(tapmask + (int64_t)g * grid, (int)grid, tile_order + (int64_t)g * grid);
       PCC_CHECK_LAUNCH("tile_rank_kernel");

@@ -53,23 +53,10 @@ def measure_classes(device="cuda:0", radius=252.0, grid=1024, reps=5, profile=Fa
     cand = m1.expand(3)                         # generative candidates of the last decoder stage (~4 M)
     n0, n1, nc = m0.n, m1.n, cand.n
     out = []
-    reps = 1 if profile else reps
-    if profile:
-        torch.cuda.synchronize()
-        torch.cuda.cudart().cudaProfilerStart()
+    todo = []  # everything is prepared first, so that a profiler range holds exactly one execution per class
 
     def add(name, kernels, units, nbytes, fn, setup=None):
-        if profile:  # exactly one execution inside the profiler range
-            if setup is not None:
-                setup()
-            fn()
-            torch.cuda.synchronize()
-            ms = float("nan")
-        else:
-            ms = _time(fn, reps, setup)
-        gbs = nbytes / (ms * 1e-3) / 1e9 if ms == ms else float("nan")
-        out.append({"class": name, "kernels": kernels, "units": units, "bytes": nbytes, "ms": ms, "gbs": gbs,
-                    "frac": gbs / hbm_gbs if gbs == gbs else None})
+        todo.append((name, kernels, units, nbytes, fn, setup))
 
     def fresh(keys, ts):
         return ops.CoordMap(keys, ts, True, 1)
@@ -138,6 +125,25 @@ def measure_classes(device="cuda:0", radius=252.0, grid=1024, reps=5, profile=Fa
         b = torch.zeros((1, cout)).to(device)
         add(f"small-channel conv {cin}->{cout} ({tag})", kern, pairs, 4.0 * (pairs * cin + m.n * cout) + 8.0 * pairs,
             lambda f=f, kmap=kmap, w=w, b=b: ops.conv(f, kmap, w, b, mode=ops.MODE_EXACT))
+    if profile:
+        for _, _, _, _, fn, setup in todo:  # warm (allocator, lazy module loading) outside the range
+            if setup is not None:
+                setup()
+            fn()
+        torch.cuda.synchronize()
+        torch.cuda.cudart().cudaProfilerStart()
+    for name, kernels, units, nbytes, fn, setup in todo:
+        if profile:
+            if setup is not None:
+                setup()
+            fn()
+            torch.cuda.synchronize()
+            ms = float("nan")
+        else:
+            ms = _time(fn, reps, setup)
+        gbs = nbytes / (ms * 1e-3) / 1e9 if ms == ms else float("nan")
+        out.append({"class": name, "kernels": kernels, "units": units, "bytes": nbytes, "ms": ms, "gbs": gbs,
+                    "frac": gbs / hbm_gbs if gbs == gbs else None})
     if profile:
         torch.cuda.synchronize()
         torch.cuda.cudart().cudaProfilerStop()
