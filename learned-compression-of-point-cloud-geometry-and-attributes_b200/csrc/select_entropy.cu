@@ -47,34 +47,56 @@ __global__ void gather_rows_kernel(const float* __restrict__ in, int c, const in
 // turns the gather into one 4-byte read per pair.  fp32 throughout, but the sum over ci is taken
 // before the sum over k — a different rounding order than the exact path's single (k, ci) FMA
 // chain, so this form serves the tolerance mode (PCC_MODE_TF32) only.
-constexpr int HP_ROWS = 64;   // rows per block
+constexpr int HP_ROWS = 128;  // rows per block
 constexpr int HP_K = 32;      // padded offsets per row of P
+constexpr int HP_RPW = HP_ROWS / 8;  // rows per warp
 
+// lane = offset k, warp w = rows 16 w .. 16 w + 15 of the block's 128: per four input channels a thread reads its
+// four weights (conflict-free, 32 consecutive floats per channel) and one broadcast float4 per row, for 64 FMAs —
+// 0.3 shared-memory loads per FMA (the first version, one thread per output with two loads per FMA, spent 4 ms per
+// frame on the three heads; ncu launch list profiles/r02_launch_summary_tf32.txt).  Same ascending-ci FMA chain.
 __global__ void __launch_bounds__(256)
 head_project_kernel(const float* __restrict__ in, int64_t n, int cin, const float* __restrict__ w, int K, int cout,
                     float* __restrict__ P) {
-  extern __shared__ float hp_smem[];
+  extern __shared__ __align__(16) float hp_smem[];
   float* w_s = hp_smem;                 // [cin][HP_K]
-  float* x_s = hp_smem + cin * HP_K;    // [HP_ROWS][cin + 1]
+  float* x_s = hp_smem + cin * HP_K;    // [HP_ROWS][cin + 4]
+  const int pitch = cin + 4;
   const int tid = threadIdx.x;
   for (int e = tid; e < cin * HP_K; e += 256) {
     const int ci = e / HP_K, k = e % HP_K;
     w_s[e] = k < K ? __ldg(w + ((int64_t)k * cin + ci) * cout) : 0.f;
   }
   const int64_t r0 = (int64_t)blockIdx.x * HP_ROWS;
-  for (int e = tid; e < HP_ROWS * cin; e += 256) {
-    const int r = e / cin, c = e % cin;
-    x_s[r * (cin + 1) + c] = r0 + r < n ? __ldg(in + (r0 + r) * cin + c) : 0.f;
+  const int q = cin / 4;  // float4 per row (cin % 4 == 0 is required by the caller)
+  for (int e = tid; e < HP_ROWS * q; e += 256) {
+    const int r = e / q, c4 = e % q;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r0 + r < n) v = __ldg(reinterpret_cast<const float4*>(in + (r0 + r) * cin) + c4);
+    *reinterpret_cast<float4*>(x_s + r * pitch + 4 * c4) = v;
   }
   __syncthreads();
-  const int k = tid % HP_K;
-  for (int r = tid / HP_K; r < HP_ROWS; r += 256 / HP_K) {
-    if (r0 + r >= n) break;
-    float acc = 0.f;
-    const float* xr = x_s + r * (cin + 1);
-#pragma unroll 8
-    for (int ci = 0; ci < cin; ++ci) acc = fmaf(xr[ci], w_s[ci * HP_K + k], acc);
-    P[(r0 + r) * HP_K + k] = acc;
+  const int k = tid & 31, wrp = tid >> 5;
+  float acc[HP_RPW];
+#pragma unroll
+  for (int j = 0; j < HP_RPW; ++j) acc[j] = 0.f;
+  const float* xb = x_s + (wrp * HP_RPW) * pitch;
+  for (int ci = 0; ci < cin; ci += 4) {
+    const float w0 = w_s[(ci + 0) * HP_K + k], w1 = w_s[(ci + 1) * HP_K + k];
+    const float w2 = w_s[(ci + 2) * HP_K + k], w3 = w_s[(ci + 3) * HP_K + k];
+#pragma unroll
+    for (int j = 0; j < HP_RPW; ++j) {
+      const float4 x = *reinterpret_cast<const float4*>(xb + j * pitch + ci);
+      acc[j] = fmaf(x.x, w0, acc[j]);
+      acc[j] = fmaf(x.y, w1, acc[j]);
+      acc[j] = fmaf(x.z, w2, acc[j]);
+      acc[j] = fmaf(x.w, w3, acc[j]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < HP_RPW; ++j) {
+    const int64_t r = r0 + wrp * HP_RPW + j;
+    if (r < n) P[r * HP_K + k] = acc[j];
   }
 }
 
@@ -474,10 +496,11 @@ int pcc_conv_head0(const float* in, int64_t n_in, int32_t cin, const float* weig
   if (n_out == 0) return PCC_OK;
   PCC_REQUIRE(in && weight && nbr && out && ws, "null pointer");
   PCC_REQUIRE(cin > 0 && cout > 0 && K > 0 && K <= 27 && nbr_stride >= n_out, "bad shape");
+  PCC_REQUIRE(cin % 4 == 0 && (reinterpret_cast<uintptr_t>(in) & 15) == 0, "cin must be a multiple of 4 and `in` 16-byte aligned");
   PCC_REQUIRE(ws_bytes >= pcc_conv_head0_ws_bytes(n_in), "workspace too small");
   cudaStream_t st = (cudaStream_t)stream;
   float* P = reinterpret_cast<float*>(ws);
-  const size_t smem = ((size_t)cin * HP_K + (size_t)HP_ROWS * (cin + 1)) * sizeof(float);
+  const size_t smem = ((size_t)cin * HP_K + (size_t)HP_ROWS * (cin + 4)) * sizeof(float);
   PCC_REQUIRE(smem <= 96 * 1024, "cin too large for the projection tile");
   static bool attr_done = false;
   if (!attr_done) {
