@@ -10,6 +10,7 @@
 //
 // Roofline: FP32 FMA pipe for cin, cout >= 32 (148 SMs x 128 lanes x 2 flop x clock); the
 // gathers are served by L2 because rows are in lexicographic order.
+#include <cuda.h>
 #include <stdlib.h>
 
 #include "pcc_common.cuh"
@@ -47,7 +48,7 @@ struct ConvParams {
   const int32_t* res_rows;
   const int32_t* order;
   float* out;
-  int64_t nbr_stride, n_out, out_stride;
+  int64_t nbr_stride, n_out, out_stride, n_in;
   int cin, cout, K, act, film_c, flags;
   float slope;
   // offset group of this launch (kernel maps with n_groups > 1: one launch per group, chained through
@@ -109,7 +110,12 @@ __device__ __forceinline__ void ffma2(unsigned long long& d, unsigned long long 
 // One pipeline stage of the register-tile loop: TK input channels of the staged rows (a: [CE_TM][TK + 4]) times the
 // staged weight slice (b: [TK][TN]) into the thread's 8 x CN accumulators, ascending ci.  Shared by the cp.async
 // kernel and the bulk-copy kernel below, so both issue the same FMA chain.
-template <int TN, int TK, bool PK>
+// SW128 = false: a is [CE_TM][TK + 4] (padded rows), rbase = the thread's first row; its rows are rbase + 4 i.
+// SW128 = true (the TMA kernel): a is the dense [CE_TM][32] tile in the TMA unit's SWIZZLE_128B layout — the 16-byte
+// chunk c of row r sits at chunk c ^ (r % 8) — which is also what keeps the four row-lanes of a warp (rows r, r+1,
+// r+2, r+3) on different banks without padding.  rbase then is the float index 32 r0 + 4 (r0 % 8) of the thread's
+// first row r0 (r0 % 8 < 4): chunk c of row r0 + 4 i is at  (rbase ^ 4 (c ^ 4 (i & 1))) + 128 i.
+template <int TN, int TK, bool PK, bool SW128 = false>
 __device__ __forceinline__ void exact_stage_fma(const float* __restrict__ sa, const float* __restrict__ sb, int rbase,
                                                 int cbase, float (&acc)[8][TN / 16],
                                                 unsigned long long (&acc2)[8][PK ? TN / 32 : 1]) {
@@ -123,7 +129,9 @@ __device__ __forceinline__ void exact_stage_fma(const float* __restrict__ sa, co
     float a[8][AV];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const float4 v = *reinterpret_cast<const float4*>(sa + (rbase + 4 * i) * AP + kv * AV);
+      const float* ap = SW128 ? sa + ((rbase ^ (4 * (kv ^ (4 * (i & 1))))) + 128 * i)
+                              : sa + (rbase + 4 * i) * AP + kv * AV;
+      const float4 v = *reinterpret_cast<const float4*>(ap);
       a[i][0] = v.x; a[i][1] = v.y; a[i][2] = v.z; a[i][3] = v.w;
     }
 #pragma unroll
@@ -548,6 +556,230 @@ static int exact_bulk() {
 }
 
 // ---------------------------------------------------------------------------------------------
+// TMA producer (cin % 32 == 0, cout % 4 == 0): the gathered rows of a stage arrive by 32
+// cp.async.bulk.tensor ... tile::gather4 instructions (four rows of the feature matrix by row index, 128 bytes
+// each; an index of -1 — a missing neighbour — is out of bounds and is zero-filled by the TMA unit), the weight
+// slice by ONE tiled load; lanes 0-3 of each warp issue one gather4 each, thread 0 the weight tile and the
+// barrier's expect_tx.  34 producer instructions per CTA and stage instead of 160 bulk copies (or 2048 cp.async lane
+// operations), no per-lane address arithmetic.  Same tile, same columns per thread, same exact_stage_fma: the FMA
+// chain of every output element is unchanged, so results are bit-identical.  The gathered tile is the dense
+// [128][32] SWIZZLE_128B layout (TMA destinations must be 128-byte aligned, so rows cannot be padded); the swizzle
+// doubles as the bank-conflict cure, at the price of one XOR per shared-memory address (exact_stage_fma).
+__device__ __forceinline__ void tma_gather4(uint32_t dst, const void* desc, uint32_t bar, int c0, int r0, int r1, int r2,
+                                            int r3) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile::gather4.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];\n" ::"r"(dst), "l"(desc), "r"(bar), "r"(c0), "r"(r0), "r"(r1), "r"(r2),
+      "r"(r3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_tile_2d(uint32_t dst, const void* desc, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];\n" ::"r"(dst), "l"(desc), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+
+template <int TN>
+struct TmaSmem {
+  float a[CE_STAGES][CE_TM * CE_TK];  // 16 KB per stage, 1024-byte aligned: SWIZZLE_128B atoms of 8 rows
+  float b[CE_STAGES][CE_TK][TN];
+  uint64_t full[CE_STAGES];
+};
+
+template <int TN>
+__global__ void __launch_bounds__(CE_THREADS, 2)
+conv_exact_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
+                      const ConvParams p) {
+  constexpr int TK = CE_TK;
+  constexpr int CN = TN / 16;
+  constexpr int CP = CN / 2;
+  static_assert(CN % 2 == 0, "packed accumulators");
+  extern __shared__ unsigned char smem_tma_raw[];
+  // the swizzle pattern is a function of the shared-memory address: the tile must start on a 1024-byte boundary
+  unsigned char* smem_tma = smem_tma_raw + ((1024u - (smem_u32(smem_tma_raw) & 1023u)) & 1023u);
+  TmaSmem<TN>& sm = *reinterpret_cast<TmaSmem<TN>*>(smem_tma);
+
+  const int tid = threadIdx.x;
+  const int lane = tid & 31, wid = tid >> 5;
+  const int tx = lane & 7, ty = lane >> 3;
+  const int rbase = (wid >> 1) * 32 + ty;  // rows rbase + 4 i
+  const int cbase = (wid & 1) * (TN / 2) + tx * (CN == 8 ? 4 : CN);
+  const unsigned tile = p.tile_order ? (unsigned)__ldg(p.tile_order + blockIdx.x) : blockIdx.x;
+  const int64_t tile_base = (int64_t)tile * CE_TM;
+  const int co_base = blockIdx.y * TN;
+  const int nchunks = p.cin / TK;
+  const uint32_t mask = p.tapmask ? (p.tapmask[tile] & p.kbits) : p.kbits;
+  const int nsteps = __popc(mask) * nchunks;
+  if (nsteps == 0 && !p.first && !p.last) return;  // CTA-uniform
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < CE_STAGES; ++s) mbar_init(&sm.full[s], 1);  // thread 0's expect_tx arrival
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  __syncthreads();
+
+  float acc[8][CN];
+  unsigned long long acc2[8][CP];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+#pragma unroll
+    for (int c = 0; c < CN; ++c) acc[i][c] = 0.0f;
+#pragma unroll
+    for (int c = 0; c < CP; ++c) acc2[i][c] = 0ull;
+  }
+  if (!p.first) {  // continue the FMA chains from the previous group's partial sums
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int64_t t = tile_base + rbase + 4 * i;
+      if (t >= p.n_out) continue;
+      const int64_t o = p.order ? (int64_t)__ldg(p.order + t) : t;
+#pragma unroll
+      for (int c = 0; c < CN; ++c) {
+        const int col = co_base + cbase + ((CN == 8) ? ((c >> 2) * 32 + (c & 3)) : c);
+        if (col < p.cout) acc[i][c] = p.out[o * p.out_stride + col];
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int c = 0; c < CP; ++c) acc2[i][c] = pack2(acc[i][2 * c], acc[i][2 * c + 1]);
+  }
+
+  // producer cursor: lanes 0-3 of warp w hold the kernel-map entries of tile rows 16 w + 4 lane .. + 3 (one gather
+  // group) for the offset being issued; they are re-read for the next active offset right after its last chunk
+  // went out, a whole stage before they are needed
+  uint32_t pmask = mask;
+  int pk = pmask ? (__ffs(pmask) - 1) : 0;
+  int pchunk = 0;
+  const int grp = wid * 4 + (lane & 3);  // gather group issued by this lane (lanes 0-3)
+  int idx[4];
+  auto load_idx = [&](int k) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t t = tile_base + 4 * grp + j;
+      idx[j] = (lane < 4 && t < p.n_out) ? __ldg(p.nbr + (int64_t)k * p.nbr_stride + t) : -1;
+    }
+  };
+  load_idx(pk);
+  constexpr uint32_t STAGE_TX = CE_TM * TK * 4u + TK * TN * 4u;  // the TMA unit counts whole boxes, zero fill included
+
+  auto issue = [&](int stage) {
+    const uint32_t bar = smem_u32(&sm.full[stage]);
+    if (tid == 0) {
+      mbar_expect_tx(&sm.full[stage], STAGE_TX);
+      tma_tile_2d(smem_u32(&sm.b[stage][0][0]), &tm_b, bar, co_base, pk * p.cin + pchunk * TK);
+    }
+    if (lane < 4)
+      tma_gather4(smem_u32(&sm.a[stage][grp * 4 * TK]), &tm_a, bar, pchunk * TK, idx[0], idx[1], idx[2], idx[3]);
+    if (++pchunk == nchunks) {
+      pchunk = 0;
+      pmask &= pmask - 1;
+      pk = pmask ? (__ffs(pmask) - 1) : 0;
+      if (pmask) load_idx(pk);
+    }
+  };
+
+#pragma unroll
+  for (int s = 0; s < CE_STAGES - 1; ++s)
+    if (s < nsteps) issue(s);
+
+  const int aidx = rbase * TK + 4 * ty;  // float index of the thread's first row in the swizzled tile (see exact_stage_fma)
+  for (int s = 0; s < nsteps; ++s) {
+    const int st = s % CE_STAGES;
+    mbar_wait(&sm.full[st], (uint32_t)((s / CE_STAGES) & 1));  // this stage's copies have landed
+    __syncthreads();  // every warp is done with step s - 1: its slot may be refilled
+    if (s + CE_STAGES - 1 < nsteps) issue((s + CE_STAGES - 1) % CE_STAGES);
+    exact_stage_fma<TN, TK, true, true>(&sm.a[st][0], &sm.b[st][0][0], aidx, cbase, acc, acc2);
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int c = 0; c < CP; ++c) unpack2(acc2[i][c], acc[i][2 * c], acc[i][2 * c + 1]);
+
+  // ---- epilogue: bias -> activation -> FiLM -> residual -> store
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int64_t t = tile_base + rbase + 4 * i;  // tile row -> output row
+    if (t >= p.n_out) continue;
+    const int64_t o = p.order ? (int64_t)__ldg(p.order + t) : t;
+    int64_t frow = o, rrow = o;
+    if (p.film_c && p.film_rows) frow = __ldg(p.film_rows + o);
+    if (p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
+#pragma unroll
+    for (int c = 0; c < CN; ++c) {
+      const int col = co_base + cbase + ((CN == 8) ? ((c >> 2) * 32 + (c & 3)) : c);
+      if (col >= p.cout) continue;
+      if (p.last)
+        conv_epilogue(p, o, frow, rrow, col, acc[i][c]);
+      else
+        p.out[o * p.out_stride + col] = acc[i][c];
+    }
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn exact_encode_tiled() {
+  static EncodeTiledFn fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      f = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(f);
+  }();
+  return fn;
+}
+
+// fp32 matrix [rows x cols] row-major, box = box_rows x box_cols, optional SWIZZLE_128B, out-of-bounds elements read as zero
+static int exact_map_2d(CUtensorMap* m, const float* ptr, int64_t rows, int64_t cols, int box_rows, int box_cols,
+                        bool sw128) {
+  EncodeTiledFn enc = exact_encode_tiled();
+  if (!enc) return PCC_ERR_CUDA;
+  const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t gstr[1] = {(cuuint64_t)cols * 4};
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1u, 1u};
+  const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), gdim, gstr, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, sw128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? PCC_OK : PCC_ERR_CUDA;
+}
+
+// -> PCC_OK when launched; 1 when the tensor maps cannot describe this call (the caller then uses another producer)
+template <int TN>
+static int launch_exact_tma(const ConvParams& p, int64_t n_in, cudaStream_t st) {
+  if (n_in <= 0 || n_in >= (1ll << 31) || (p.cout * 4) % 16 != 0 || (reinterpret_cast<uintptr_t>(p.in) & 15) != 0 ||
+      (reinterpret_cast<uintptr_t>(p.weight) & 15) != 0)
+    return 1;
+  CUtensorMap tm_a, tm_b;
+  if (exact_map_2d(&tm_a, p.in, n_in, p.cin, 1, CE_TK, true) != PCC_OK) return 1;
+  if (exact_map_2d(&tm_b, p.weight, (int64_t)p.K * p.cin, p.cout, CE_TK, TN, false) != PCC_OK) return 1;
+  const size_t smem = sizeof(TmaSmem<TN>) + 1024;  // + slack for the 1024-byte alignment of the tile
+  dim3 grid((unsigned)ceil_div(p.n_out, CE_TM), (unsigned)ceil_div(p.cout, TN));
+  static const cudaError_t attr = cudaFuncSetAttribute(conv_exact_tma_kernel<TN>,
+                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  PCC_CHECK_CUDA(attr);
+  conv_exact_tma_kernel<TN><<<grid, CE_THREADS, smem, st>>>(tm_a, tm_b, p);
+  PCC_CHECK_LAUNCH("conv_exact_tma_kernel");
+  return PCC_OK;
+}
+
+// PCC_EXACT_TMA: 0 = never, 1 = 128-wide tiles only, 2 = 128- and 64-wide tiles (default).  Measured on the
+// 799,458-point frame, same box: dominant-kernel fraction 0.590 (off) / 0.610 (1) / 0.624 (2), 4.40 / 4.54 / 4.62 M
+// points/s; every >= 64-channel layer gains 4-7 %.
+static int exact_tma() {
+  static int v = [] {
+    const char* e = getenv("PCC_EXACT_TMA");
+    return e ? atoi(e) : 2;
+  }();
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Narrow-output variant (cout <= 4: occupancy / quality / colour heads).  With so few output
 // channels the register-tile kernel above spends its time on padded columns; here one thread owns
 // one output row and all (<= 4) channels, so the arithmetic is negligible and the kernel runs at
@@ -716,6 +948,13 @@ static int launch_exact(const ConvParams& p, cudaStream_t st) {
   // measured on the 799,458-point frame (profiles/r02_*): the bulk-copy producer is 2 % faster on the 128-wide
   // tiles (1.19 M x 128 -> 128: 14.44 -> 14.18 ms) and 7 % slower on the 64-wide ones (twice the copies per FMA), so
   // only the 128-wide kernel uses it; PCC_EXACT_BULK=2 forces it for 64- and 32-wide tiles too
+  if constexpr (TN >= 64) {
+    const int tma = exact_tma();
+    if (vec && f2 != 0 && p.cin % CE_TK == 0 && (tma >= 2 || (tma == 1 && TN == 128))) {
+      const int rc = launch_exact_tma<TN>(p, p.n_in, st);
+      if (rc <= 0) return rc;  // launched, or a CUDA error; 1 = tensor maps not applicable -> next producer
+    }
+  }
   if constexpr (TN >= 32) {
     const int bulk = exact_bulk();
     if (vec && f2 != 0 && p.cin % CE_TK == 0 && (bulk >= 2 || (bulk == 1 && TN == 128)))
@@ -744,6 +983,7 @@ int conv_exact(const pcc_conv_args* a, cudaStream_t st) {
   p.in = a->in; p.weight = a->weight; p.bias = a->bias; p.nbr = a->nbr; p.tapmask = a->tapmask;
   p.film = a->film; p.film_rows = a->film_rows; p.residual = a->residual; p.res_rows = a->res_rows;
   p.order = a->order; p.out = a->out; p.nbr_stride = a->nbr_stride; p.n_out = a->n_out; p.out_stride = a->out_stride;
+  p.n_in = a->n_in;
   p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope; p.flags = a->flags;
   const uint32_t kfull = p.K >= 32 ? 0xffffffffu : ((1u << p.K) - 1u);
   p.tile_order = a->tile_order;
