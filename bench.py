@@ -243,12 +243,15 @@ def roofline_pass(model, x_dev, q_dev, peaks, clocks, dump=None):
         peak = 148 * 128 * 2 * mhz * 1e6 / 1e12
         bound, src = "fp32_fma", f"148 SM x 128 FMA x 2 x {mhz:g} MHz (no measured FP32 peak exists)"
     roof = {"bound": bound, "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-            "traffic": None, "kernel": "conv_tf32_kernel" if tf32 else "conv_exact_kernel<128>",
+            "traffic": None,
+            "kernel": "conv_tf32_kernel" if tf32 else "conv_exact_tma_kernel<128,8> / <64,8> (every launch with Cin, Cout >= 64)",
             "launches": len(dom), "avg_launch_ms": t_ms / len(dom), "peak_source": src,
             "share_of_conv_time": t_ms / sum(r["ms"] for r in recs),
             "hbm_gbs_algorithmic": sum(conv_bytes(r) for r in dom) / (t_ms * 1e-3) / 1e9}
     try:  # DRAM traffic of one captured launch (ncu --set full), committed under profiles/
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_traffic.json")) as f:
+        prof = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles")
+        name = "r02_traffic.json" if os.path.exists(os.path.join(prof, "r02_traffic.json")) else "r01_traffic.json"
+        with open(os.path.join(prof, name)) as f:
             tr = json.load(f)["tf32" if tf32 else "exact"]
         roof["traffic"] = tr["traffic_bytes"]
         roof["traffic_detail"] = {k: tr[k] for k in ("launch", "algorithmic_bytes", "source")}

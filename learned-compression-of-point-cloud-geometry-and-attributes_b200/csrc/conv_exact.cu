@@ -115,11 +115,10 @@ __device__ __forceinline__ void ffma2(unsigned long long& d, unsigned long long 
 // chunk c of row r sits at chunk c ^ (r % 8) — which is also what keeps the four row-lanes of a warp (rows r, r+1,
 // r+2, r+3) on different banks without padding.  rbase then is the float index 32 r0 + 4 (r0 % 8) of the thread's
 // first row r0 (r0 % 8 < 4): chunk c of row r0 + 4 i is at  (rbase ^ 4 (c ^ 4 (i & 1))) + 128 i.
-template <int TN, int TK, bool PK, bool SW128 = false>
+template <int TN, int TK, bool PK, bool SW128 = false, int CN = TN / 16>
 __device__ __forceinline__ void exact_stage_fma(const float* __restrict__ sa, const float* __restrict__ sb, int rbase,
-                                                int cbase, float (&acc)[8][TN / 16],
-                                                unsigned long long (&acc2)[8][PK ? TN / 32 : 1]) {
-  constexpr int CN = TN / 16;
+                                                int cbase, float (&acc)[8][CN],
+                                                unsigned long long (&acc2)[8][PK ? CN / 2 : 1]) {
   constexpr int AV = 4;
   constexpr int CP = PK ? CN / 2 : 1;
   constexpr int AP = TK + 4;
@@ -587,12 +586,18 @@ struct TmaSmem {
   uint64_t full[CE_STAGES];
 };
 
-template <int TN>
-__global__ void __launch_bounds__(CE_THREADS, 2)
+// CN: output channels per thread.  16 row-threads x TN / CN column-threads: <128, 8> and <64, 4> are the 256-thread
+// shapes of conv_exact_kernel; <64, 8> covers a 64-wide tile with 128 threads that keep the 8 x 8 register tile
+// (a third fewer shared-memory operand bytes per FMA than the 8 x 4 tile), three CTAs per SM.
+template <int TN, int CN>
+__global__ void __launch_bounds__(16 * TN / CN, (16 * TN / CN) == 128 ? 3 : 2)
 conv_exact_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                       const ConvParams p) {
   constexpr int TK = CE_TK;
-  constexpr int CN = TN / 16;
+  constexpr int NT = 16 * TN / CN;     // threads
+  constexpr int WCOLS = 8 * CN;        // columns a warp covers (CN == 8: two quads 32 apart)
+  constexpr int NWX = TN / WCOLS;      // warps side by side
+  constexpr int GPW = 32 / (NT / 32);  // gather groups issued per warp
   constexpr int CP = CN / 2;
   static_assert(CN % 2 == 0, "packed accumulators");
   extern __shared__ unsigned char smem_tma_raw[];
@@ -603,8 +608,8 @@ conv_exact_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
   const int tid = threadIdx.x;
   const int lane = tid & 31, wid = tid >> 5;
   const int tx = lane & 7, ty = lane >> 3;
-  const int rbase = (wid >> 1) * 32 + ty;  // rows rbase + 4 i
-  const int cbase = (wid & 1) * (TN / 2) + tx * (CN == 8 ? 4 : CN);
+  const int rbase = (wid / NWX) * 32 + ty;  // rows rbase + 4 i
+  const int cbase = (wid % NWX) * WCOLS + tx * (CN == 8 ? 4 : CN);
   const unsigned tile = p.tile_order ? (unsigned)__ldg(p.tile_order + blockIdx.x) : blockIdx.x;
   const int64_t tile_base = (int64_t)tile * CE_TM;
   const int co_base = blockIdx.y * TN;
@@ -647,19 +652,19 @@ conv_exact_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
       for (int c = 0; c < CP; ++c) acc2[i][c] = pack2(acc[i][2 * c], acc[i][2 * c + 1]);
   }
 
-  // producer cursor: lanes 0-3 of warp w hold the kernel-map entries of tile rows 16 w + 4 lane .. + 3 (one gather
-  // group) for the offset being issued; they are re-read for the next active offset right after its last chunk
+  // producer cursor: lanes 0 .. GPW-1 of warp w hold the kernel-map entries of one gather group each (tile rows
+  // 4 (GPW w + lane) .. + 3) for the offset being issued; they are re-read for the next active offset right after its last chunk
   // went out, a whole stage before they are needed
   uint32_t pmask = mask;
   int pk = pmask ? (__ffs(pmask) - 1) : 0;
   int pchunk = 0;
-  const int grp = wid * 4 + (lane & 3);  // gather group issued by this lane (lanes 0-3)
+  const int grp = wid * GPW + (lane % GPW);  // gather group issued by this lane (lanes < GPW)
   int idx[4];
   auto load_idx = [&](int k) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int64_t t = tile_base + 4 * grp + j;
-      idx[j] = (lane < 4 && t < p.n_out) ? __ldg(p.nbr + (int64_t)k * p.nbr_stride + t) : -1;
+      idx[j] = (lane < GPW && t < p.n_out) ? __ldg(p.nbr + (int64_t)k * p.nbr_stride + t) : -1;
     }
   };
   load_idx(pk);
@@ -671,7 +676,7 @@ conv_exact_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
       mbar_expect_tx(&sm.full[stage], STAGE_TX);
       tma_tile_2d(smem_u32(&sm.b[stage][0][0]), &tm_b, bar, co_base, pk * p.cin + pchunk * TK);
     }
-    if (lane < 4)
+    if (lane < GPW)
       tma_gather4(smem_u32(&sm.a[stage][grp * 4 * TK]), &tm_a, bar, pchunk * TK, idx[0], idx[1], idx[2], idx[3]);
     if (++pchunk == nchunks) {
       pchunk = 0;
@@ -691,7 +696,7 @@ conv_exact_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
     mbar_wait(&sm.full[st], (uint32_t)((s / CE_STAGES) & 1));  // this stage's copies have landed
     __syncthreads();  // every warp is done with step s - 1: its slot may be refilled
     if (s + CE_STAGES - 1 < nsteps) issue((s + CE_STAGES - 1) % CE_STAGES);
-    exact_stage_fma<TN, TK, true, true>(&sm.a[st][0], &sm.b[st][0][0], aidx, cbase, acc, acc2);
+    exact_stage_fma<TN, TK, true, true, CN>(&sm.a[st][0], &sm.b[st][0][0], aidx, cbase, acc, acc2);
   }
 #pragma unroll
   for (int i = 0; i < 8; ++i)
@@ -750,7 +755,7 @@ static int exact_map_2d(CUtensorMap* m, const float* ptr, int64_t rows, int64_t 
 }
 
 // -> PCC_OK when launched; 1 when the tensor maps cannot describe this call (the caller then uses another producer)
-template <int TN>
+template <int TN, int CN>
 static int launch_exact_tma(const ConvParams& p, int64_t n_in, cudaStream_t st) {
   if (n_in <= 0 || n_in >= (1ll << 31) || (p.cout * 4) % 16 != 0 || (reinterpret_cast<uintptr_t>(p.in) & 15) != 0 ||
       (reinterpret_cast<uintptr_t>(p.weight) & 15) != 0)
@@ -760,10 +765,10 @@ static int launch_exact_tma(const ConvParams& p, int64_t n_in, cudaStream_t st) 
   if (exact_map_2d(&tm_b, p.weight, (int64_t)p.K * p.cin, p.cout, CE_TK, TN, false) != PCC_OK) return 1;
   const size_t smem = sizeof(TmaSmem<TN>) + 1024;  // + slack for the 1024-byte alignment of the tile
   dim3 grid((unsigned)ceil_div(p.n_out, CE_TM), (unsigned)ceil_div(p.cout, TN));
-  static const cudaError_t attr = cudaFuncSetAttribute(conv_exact_tma_kernel<TN>,
+  static const cudaError_t attr = cudaFuncSetAttribute(conv_exact_tma_kernel<TN, CN>,
                                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   PCC_CHECK_CUDA(attr);
-  conv_exact_tma_kernel<TN><<<grid, CE_THREADS, smem, st>>>(tm_a, tm_b, p);
+  conv_exact_tma_kernel<TN, CN><<<grid, 16 * TN / CN, smem, st>>>(tm_a, tm_b, p);
   PCC_CHECK_LAUNCH("conv_exact_tma_kernel");
   return PCC_OK;
 }
@@ -951,7 +956,21 @@ static int launch_exact(const ConvParams& p, cudaStream_t st) {
   if constexpr (TN >= 64) {
     const int tma = exact_tma();
     if (vec && f2 != 0 && p.cin % CE_TK == 0 && (tma >= 2 || (tma == 1 && TN == 128))) {
-      const int rc = launch_exact_tma<TN>(p, p.n_in, st);
+      // 64-wide tiles: 128 threads with 8 x 8 register tiles (3 CTAs per SM) for the large same-map layers, where
+      // they are 3.8 % faster (3 x 64->64 on the 3.98 M candidates: 36.7 -> 35.3 ms); 256 threads with 8 x 4 tiles
+      // elsewhere (short tiles — the generative transposed convolution has 1-8 active offsets per tile — and
+      // surface levels run 5-30 % faster on them).  PCC_EXACT_TMA64 = 8 / 4 forces one shape, 0 = this rule.
+      static const int cn64 = [] {
+        const char* e = getenv("PCC_EXACT_TMA64");
+        return e ? atoi(e) : 0;
+      }();
+      int rc;
+      if constexpr (TN == 64)
+        rc = (cn64 == 8 || (cn64 == 0 && p.n_in == p.n_out && p.n_out >= (2ll << 20)))
+                 ? launch_exact_tma<64, 8>(p, p.n_in, st)
+                 : launch_exact_tma<64, 4>(p, p.n_in, st);
+      else
+        rc = launch_exact_tma<TN, TN / 16>(p, p.n_in, st);
       if (rc <= 0) return rc;  // launched, or a CUDA error; 1 = tensor maps not applicable -> next producer
     }
   }
@@ -972,7 +991,12 @@ static int conv_exact_group(const pcc_conv_args* a, const ConvParams& p, cudaStr
   // a grid that cannot fill 2 CTAs on every SM is split further along the output channels
   const int64_t tiles = ceil_div(p.n_out, CE_TM);
   const bool small_grid = tiles * ceil_div(p.cout, 128) < 2 * (int64_t)sm_count();
-  if (a->cout > 64 && !small_grid) return launch_exact<128>(p, st);
+  // PCC_EXACT_WIDE=0: cover wide layers with 64-wide tiles too (A/B of the 128-thread 8 x 8 kernel)
+  static const int wide = [] {
+    const char* e = getenv("PCC_EXACT_WIDE");
+    return e ? atoi(e) : 1;
+  }();
+  if (a->cout > 64 && !small_grid && wide) return launch_exact<128>(p, st);
   if (a->cout > 32) return launch_exact<64>(p, st);
   if (a->cout > 16) return launch_exact<32>(p, st);
   return launch_exact<16>(p, st);
