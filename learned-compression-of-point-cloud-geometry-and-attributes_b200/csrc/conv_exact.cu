@@ -923,6 +923,173 @@ static int launch_head(const ConvParams& p, cudaStream_t st) {
   return PCC_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Thin-input variant (cin <= 4, 27 offsets: the quality-map branch 2 -> 2 / 2 -> 16 / 2 -> 128, the condition
+// convolutions 4 -> 2 and the xyz/rgb input layer 4 -> 64).  A neighbour's whole feature row is 8 or 16 bytes, so
+// the tiled kernels spend their time staging 27 nearly empty shared-memory stages per tile.  Here one thread owns
+// one output row: it reads its 27 kernel-map entries (coalesced) and the <= 27 neighbour rows (one 8 / 16-byte
+// load each) into REGISTERS once, then walks the output channels CC at a time with the layer's weights broadcast
+// from shared memory (loaded once per CTA; CTAs stride over the tiles).  Finished columns go through a shared
+// staging tile so that the epilogue (bias, activation, FiLM, residual) and the stores run row-contiguous.
+// Same summation order as everywhere (k ascending, ci ascending, one FMA chain per output element; a missing
+// neighbour contributes fma(0, w, acc) like a zero-filled tile row), so results are bit-identical.
+template <int CIN, int CC>
+__global__ void __launch_bounds__(CE_TM, CIN * 27 + CC + 56 <= 128 ? 4 : (CIN * 27 + CC + 56 <= 184 ? 3 : 2))
+conv_thin_kernel(const ConvParams p, int tiles) {
+  constexpr int K = 27;
+  constexpr int CP = CC / 2;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int pitch = (p.cout + CC - 1) / CC * CC;               // weight row pitch: whole column passes
+  float* sw = reinterpret_cast<float*>(smem_raw);              // [K * CIN][pitch]
+  float* stg = sw + K * CIN * pitch;                           // [CE_TM][CC + 1]
+  int* srow = reinterpret_cast<int*>(stg + CE_TM * (CC + 1));  // [3][CE_TM]: output row, FiLM row, residual row
+  const int tid = threadIdx.x;
+  for (int i = tid; i < K * CIN * pitch; i += CE_TM) {
+    const int r = i / pitch, c = i - r * pitch;
+    sw[i] = c < p.cout ? __ldg(p.weight + (int64_t)r * p.cout + c) : 0.0f;
+  }
+  for (int b = blockIdx.x; b < tiles; b += gridDim.x) {
+    const unsigned tile = p.tile_order ? (unsigned)__ldg(p.tile_order + b) : (unsigned)b;
+    const int64_t tile_base = (int64_t)tile * CE_TM;
+    const uint32_t mask = p.tapmask ? (p.tapmask[tile] & p.kbits) : p.kbits;
+    if (mask == 0 && !p.first && !p.last) continue;  // CTA-uniform
+    const int64_t t = tile_base + tid;
+    const bool valid = t < p.n_out;
+    const int64_t o = valid ? (p.order ? (int64_t)__ldg(p.order + t) : t) : -1;
+    __syncthreads();  // weights visible (first tile) / the previous tile's staging reads are done
+    {
+      int frow = (int)o, rrow = (int)o;
+      if (valid && p.film_c && p.film_rows) frow = __ldg(p.film_rows + o);
+      if (valid && p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
+      srow[tid] = (int)o;
+      srow[CE_TM + tid] = frow;
+      srow[2 * CE_TM + tid] = rrow;
+    }
+    // the tile rows are mask-sorted, so the 32 rows of a warp mostly share their neighbour set: offsets that no
+    // row of the warp has are skipped by the whole warp (wmask), which leaves ~45 % of the 27 on a surface
+    float x[K][CIN];
+    uint32_t wmask = 0;
+    {
+      // three straight-line phases (no branch on a loaded value), so the 27 index loads and then the <= 27 row
+      // loads are all in flight together instead of one round trip per offset
+      int ixs[K];
+#pragma unroll
+      for (int k = 0; k < K; ++k)
+        ixs[k] = (valid && ((mask >> k) & 1u)) ? __ldg(p.nbr + (int64_t)k * p.nbr_stride + t) : -1;
+#pragma unroll
+      for (int k = 0; k < K; ++k)
+        if (__ballot_sync(0xffffffffu, ixs[k] >= 0)) wmask |= 1u << k;
+#pragma unroll
+      for (int k = 0; k < K; ++k) {
+        const bool has = ixs[k] >= 0;
+        const float* src = p.in + (int64_t)(has ? ixs[k] : 0) * CIN;
+        if constexpr (CIN == 4) {
+          float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (has) v = __ldg(reinterpret_cast<const float4*>(src));
+          x[k][0] = v.x; x[k][1] = v.y; x[k][2] = v.z; x[k][3] = v.w;
+        } else if constexpr (CIN == 2) {
+          float2 v = make_float2(0.f, 0.f);
+          if (has) v = __ldg(reinterpret_cast<const float2*>(src));
+          x[k][0] = v.x; x[k][1] = v.y;
+        } else {
+#pragma unroll
+          for (int ci = 0; ci < CIN; ++ci) {
+            float v = 0.f;
+            if (has) v = __ldg(src + ci);
+            x[k][ci] = v;
+          }
+        }
+      }
+    }
+    for (int c0 = 0; c0 < p.cout; c0 += CC) {
+      float acc[CC];
+#pragma unroll
+      for (int j = 0; j < CC; ++j) acc[j] = 0.0f;
+      if (!p.first && valid) {  // continue the chains of the previous offset group
+#pragma unroll
+        for (int j = 0; j < CC; ++j)
+          if (c0 + j < p.cout) acc[j] = p.out[o * p.out_stride + c0 + j];
+      }
+      unsigned long long acc2[CP];
+#pragma unroll
+      for (int j = 0; j < CP; ++j) acc2[j] = pack2(acc[2 * j], acc[2 * j + 1]);
+#pragma unroll
+      for (int k = 0; k < K; ++k) {
+        if (!((wmask >> k) & 1u)) continue;  // warp-uniform: every lane would add fma(0, w, acc) = acc
+#pragma unroll
+        for (int ci = 0; ci < CIN; ++ci) {
+          const float* wr = sw + (k * CIN + ci) * pitch + c0;
+          const unsigned long long xx = pack2(x[k][ci], x[k][ci]);
+#pragma unroll
+          for (int j4 = 0; j4 < CC / 4; ++j4) {
+            const float4 w = *reinterpret_cast<const float4*>(wr + 4 * j4);
+            ffma2(acc2[2 * j4], xx, pack2(w.x, w.y));
+            ffma2(acc2[2 * j4 + 1], xx, pack2(w.z, w.w));
+          }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < CP; ++j) unpack2(acc2[j], acc[2 * j], acc[2 * j + 1]);
+      if (c0) __syncthreads();  // the previous pass's staging reads are done
+#pragma unroll
+      for (int j = 0; j < CC; ++j) stg[tid * (CC + 1) + j] = acc[j];
+      __syncthreads();
+      const int ncol = p.cout - c0 < CC ? p.cout - c0 : CC;
+      for (int e = tid; e < CE_TM * CC; e += CE_TM) {
+        const int r = e / CC, c = e % CC;  // CC = 32: one warp stores 128 contiguous bytes of one row
+        const int64_t orow = srow[r];
+        if (c >= ncol || orow < 0) continue;
+        const float v = stg[r * (CC + 1) + c];
+        if (p.last)
+          conv_epilogue(p, orow, srow[CE_TM + r], srow[2 * CE_TM + r], c0 + c, v);
+        else
+          p.out[orow * p.out_stride + c0 + c] = v;
+      }
+    }
+  }
+}
+
+// -> PCC_OK when launched, 1 when this call is not a thin-input shape (the caller falls through)
+template <int CIN>
+static int launch_thin_cin(const ConvParams& p, cudaStream_t st) {
+  const int cc = (p.cout > 16 && CIN <= 2) ? 32 : (p.cout > 4 ? 16 : 4);  // x[27][CIN] + CC accumulators in registers
+  const int pitch = (p.cout + cc - 1) / cc * cc;
+  const size_t smem = (size_t)27 * CIN * pitch * 4 + (size_t)CE_TM * (cc + 1) * 4 + 3 * CE_TM * 4;
+  if (smem > 96 * 1024) return 1;
+  const int tiles = (int)ceil_div(p.n_out, CE_TM);
+  const int grid = tiles < 4 * sm_count() ? tiles : 4 * sm_count();
+#define PCC_THIN_LAUNCH(CCV)                                                                                     \
+  {                                                                                                              \
+    static const cudaError_t attr = cudaFuncSetAttribute(conv_thin_kernel<CIN, CCV>,                             \
+                                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); \
+    PCC_CHECK_CUDA(attr);                                                                                        \
+    conv_thin_kernel<CIN, CCV><<<grid, CE_TM, smem, st>>>(p, tiles);                                             \
+  }
+  if (cc == 32) PCC_THIN_LAUNCH(32) else if (cc == 16) PCC_THIN_LAUNCH(16) else PCC_THIN_LAUNCH(4)
+#undef PCC_THIN_LAUNCH
+  PCC_CHECK_LAUNCH("conv_thin_kernel");
+  return PCC_OK;
+}
+
+// PCC_EXACT_THIN=0 keeps the tiled kernel with 4-channel stages for cin <= 4 (A/B timing)
+static int launch_thin(const ConvParams& p, cudaStream_t st) {
+  static const int on = [] {
+    const char* e = getenv("PCC_EXACT_THIN");
+    return e ? atoi(e) : 1;
+  }();
+  // cout > 16 stays on the tiled kernel: with x[27][cin] in registers there is no room to keep enough weight
+  // loads in flight, and the column passes run at the shared-memory latency (measured 2 -> 128 on 249,574 rows:
+  // 0.57 ms here vs 0.42 ms tiled; 4 -> 64 on 799,458 rows: 0.61 vs 0.43 ms; PCC_EXACT_THIN=2 forces them here)
+  if (!on || p.K != 27 || p.cin < 1 || p.cin > 4 || p.n_out >= (1ll << 31) - CE_TM || (p.cout > 16 && on < 2)) return 1;
+  const uintptr_t a = reinterpret_cast<uintptr_t>(p.in);
+  switch (p.cin) {
+    case 1: return launch_thin_cin<1>(p, st);
+    case 2: return (a & 7) ? 1 : launch_thin_cin<2>(p, st);
+    case 3: return launch_thin_cin<3>(p, st);
+    default: return (a & 15) ? 1 : launch_thin_cin<4>(p, st);
+  }
+}
+
 template <int TN, bool VEC, int F2, int TK = CE_TK>
 static int launch_exact_v(const ConvParams& p, cudaStream_t st) {
   const size_t smem = sizeof(ExactSmem<TN, TK>);
@@ -979,7 +1146,11 @@ static int launch_exact(const ConvParams& p, cudaStream_t st) {
     if (vec && f2 != 0 && p.cin % CE_TK == 0 && (bulk >= 2 || (bulk == 1 && TN == 128)))
       return launch_exact_bulk<TN>(p, st);
   }
-  if (p.cin <= 4 && f2 != 0)  // thin input (the Q branch, the xyz/rgb input layer): 4-channel stages
+  if (p.cin <= 4 && f2 != 0) {  // thin input (the Q branch, the xyz/rgb input layer)
+    const int rc = launch_thin(p, st);
+    if (rc <= 0) return rc;  // launched or failed; 1 = not a thin shape -> tiled kernel with 4-channel stages
+  }
+  if (p.cin <= 4 && f2 != 0)
     return vec ? launch_exact_v<TN, true, 1, 4>(p, st) : launch_exact_v<TN, false, 1, 4>(p, st);
   if (f2 != 0) return vec ? launch_exact_v<TN, true, 1>(p, st) : launch_exact_v<TN, false, 1>(p, st);
   return vec ? launch_exact_v<TN, true, 0>(p, st) : launch_exact_v<TN, false, 0>(p, st);

@@ -634,8 +634,16 @@ tile_rank_kernel(const uint32_t* __restrict__ tapmask, int tiles, int32_t* __res
   }
 }
 
-// n_groups == 0 (automatic): single-group tiles are kept when at least this share of their MACs is useful
-constexpr double AUTO_GROUP_MIN_EFFICIENCY = 0.72;  // measured break-even: three chained passes run ~20 % below one
+// n_groups == 0 (automatic).  Measured with the TMA kernel on the surface levels of the 799,458-voxel frame
+// (tools/ragged_conv_bench.py, profiles/r02_ragged_groups.txt; 128 -> 128, useful-MAC share of the mask-sorted
+// tiles with 1 / 2 / 3 groups in brackets):
+//   249,574 rows (0.858 / 0.957 / 0.986): 2.376 / 2.221 / 2.250 ms      68,423 rows (0.756 / 0.889 / 0.959):
+//   0.862 / 0.768 / 0.768 ms      17,957 rows (0.664 / 0.772 / 0.868): 0.347 / 0.361 / 0.372 ms
+// i.e. every extra chained pass costs ~4 % of the padded-MAC rate, and a map that cannot fill the GPU twice gains
+// nothing from shorter tiles.  Rule: one group when the single-group tiles are >= 90 % useful or the map has
+// fewer than 2 x SM-count tiles; two groups down to 70 %; three below.
+constexpr double AUTO_GROUP_ONE_MIN_EFFICIENCY = 0.90;
+constexpr double AUTO_GROUP_TWO_MIN_EFFICIENCY = 0.70;
 constexpr int AUTO_GROUPS = 3;
 
 template <int KS>
@@ -688,8 +696,10 @@ static int kernel_map_launch(const uint64_t* tkeys, const int32_t* tvals, uint64
     unsigned long long* h = pinned_counts() ? reinterpret_cast<unsigned long long*>(pinned_counts()) : hbuf;
     PCC_CHECK_CUDA(cudaMemcpyAsync(h, sums, 16, cudaMemcpyDeviceToHost, st));
     PCC_CHECK_CUDA(cudaStreamSynchronize(st));
-    const bool single = K < AUTO_GROUPS || (double)h[0] >= AUTO_GROUP_MIN_EFFICIENCY * (double)h[1];
-    n_groups = single ? 1 : AUTO_GROUPS;
+    const double useful = (double)h[0], padded = (double)h[1];
+    const bool single = K < AUTO_GROUPS || (int64_t)grid < 2 * (int64_t)sm_count() ||
+                        useful >= AUTO_GROUP_ONE_MIN_EFFICIENCY * padded;
+    n_groups = single ? 1 : (useful >= AUTO_GROUP_TWO_MIN_EFFICIENCY * padded ? 2 : AUTO_GROUPS);
     have_order0 = single;
     if (n_groups_used) *n_groups_used = n_groups;
   }

@@ -286,10 +286,11 @@ def tile_segment_rows():
 
 
 # Offset groups of the kernel maps (pcc_kernel_map n_groups).  None = by mode: the exact path lets the
-# library measure each 27-offset map (n_groups = 0): maps whose mask-sorted tiles use >= 72 % of
-# their MACs keep one group, ragged ones (e.g. the decoder's pruned sets under random-init weights,
-# 40-60 %) are cut into 3 groups of 9 offsets, each with its own mask-sorted tile rows (80-98 %), for
-# two extra launches per convolution.  The tensor-core kernel takes single-group maps only.
+# library measure each 27-offset map (n_groups = 0): maps whose mask-sorted tiles use >= 90 % of their MACs, and
+# maps too small to fill the GPU twice, keep one group; down to 70 % the 27 offsets are cut into 2 ranges, below
+# that (e.g. the decoder's pruned sets under random-init weights, 40-60 %) into 3, each range with its own
+# mask-sorted tile rows (89-99 %), for one or two extra chained launches per convolution (coords.cu has the
+# measurements behind the rule).  The tensor-core kernel takes single-group maps only.
 _tap_groups = int(os.environ["PCC_TAP_GROUPS"]) if "PCC_TAP_GROUPS" in os.environ else None
 AUTO_GROUPS = 3
 

@@ -91,6 +91,35 @@ def test_conv_epilogue_bitwise(pcc, oracle, cin, cout, film_c, act):
     assert np.array_equal(got.cpu().numpy().view(np.uint32), ref.astype(np.float32).view(np.uint32))
 
 
+@pytest.mark.parametrize("cin", [1, 2, 3, 4])
+@pytest.mark.parametrize("cout,groups", [(1, 1), (2, 3), (3, 1), (16, 1), (20, 3), (64, 1), (128, 1), (130, 3)])
+def test_conv_thin_input_bitwise(pcc, oracle, cin, cout, groups):
+    """cin <= 4, 27 offsets: conv_thin_kernel (neighbour rows in registers, weights in shared memory), with the
+    fused epilogue and with the offsets cut into chained groups; several tiles per CTA-stride and a ragged tail."""
+    rng = np.random.default_rng(cin * 100 + cout)
+    m, keys, cs = _setup(pcc, oracle, 4000, 24, 1, cin + 7 * cout)
+    n = m.n
+    x = rng.standard_normal((n, cin)).astype(np.float32)
+    W = rng.standard_normal((27, cin, cout)).astype(np.float32)
+    b = rng.standard_normal((1, cout)).astype(np.float32)
+    nbr = oracle.prims.kernel_map(keys, cs, oracle.prims.kernel_offsets(3))
+    ref = oracle.prims.leaky_relu(oracle.prims.conv_apply(x, nbr, W, b))
+    film = rng.standard_normal((n, 2 * cout)).astype(np.float32)
+    frows = rng.integers(-1, n, size=n).astype(np.int32)
+    g = np.where(frows[:, None] >= 0, film[np.maximum(frows, 0)], np.float32(0))
+    ref = (ref * g[:, :cout] + g[:, cout:]).astype(np.float32)
+    res = rng.standard_normal((n, cout)).astype(np.float32)
+    ref = ref + res
+    t = lambda a: torch.from_numpy(a).to(DEV)
+    km = m.kernel_map(m, 3, groups=groups)
+    assert km.n_groups == groups
+    got = pcc.ops.conv(t(x), km, t(W), t(b), act=2, film=t(film), film_rows=t(frows), residual=t(res))
+    assert np.array_equal(got.cpu().numpy().view(np.uint32), ref.view(np.uint32))
+    plain = pcc.ops.conv(t(x), km, t(W), None)
+    assert np.array_equal(plain.cpu().numpy().view(np.uint32),
+                          oracle.prims.conv_apply(x, nbr, W, None).view(np.uint32))
+
+
 def test_conv_zero_rows_and_tiny(pcc, oracle):
     m, keys, cs = _setup(pcc, oracle, 1, 2, 1, 3)
     x = torch.ones((m.n, 8), device=DEV)

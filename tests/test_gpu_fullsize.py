@@ -74,12 +74,24 @@ def test_kernel_map_properties_full_size(pcc, level0):
     tiles = (n + 127) // 128
     pad = torch.full((27, tiles * 128 - n), -1, dtype=torch.int32, device=DEV)
     active = (torch.cat([km.nbr[:, :n], pad], 1).view(27, tiles, 128) >= 0).any(dim=2)
-    assert km.n_groups == 1                                             # a surface: mask-sorted tiles are >= 72 % useful
+    assert km.n_groups == 1                                             # the input surface: mask-sorted tiles are >= 90 % useful (0.92)
     for g, (lo, hi) in enumerate(km.group_ranges()):
         assert torch.equal(torch.sort(km.order.view(km.n_groups, -1)[g].long()).values, torch.arange(n, device=DEV))
         tm = km.tapmask.view(km.n_groups, -1)[g].long()
         bits = ((tm.unsqueeze(0) >> torch.arange(27, device=DEV).unsqueeze(1)) & 1).bool()
         assert torch.equal(bits[lo:hi], active[lo:hi]) and not bool(bits[:lo].any()) and not bool(bits[hi:].any())
+
+
+def test_automatic_offset_groups_full_size(pcc, level0):
+    """pcc_kernel_map(n_groups = 0) on the surface levels of the frame: 0.92 useful -> one group; 0.86 and 0.76
+    (249,574 and 68,423 rows) -> two; 17,957 rows cannot fill the GPU twice -> one (coords.cu, measured rule)."""
+    m = level0
+    want = [1, 2, 2, 1]
+    for lv in range(4):
+        km = m.kernel_map(m, 3)
+        assert km.n_groups == want[lv], (lv, m.n, km.n_groups)
+        assert km.order.numel() == km.n_groups * m.n and km.tapmask.numel() == km.n_groups * ((m.n + 127) // 128)
+        m = m.stride2()
 
 
 @pytest.mark.parametrize("cin,cout,mode", [(64, 64, 0), (128, 128, 0), (64, 4, 0), (128, 128, 1)])
