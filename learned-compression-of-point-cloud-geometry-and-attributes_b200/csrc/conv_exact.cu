@@ -56,6 +56,7 @@ struct ConvParams {
   uint32_t kbits;   // offsets this launch may touch
   int first, last;  // first: accumulators start at 0; last: epilogue applied
   const int32_t* tile_order;  // CTA b works on tile tile_order[b] (longest tiles first), NULL = identity
+  int vec4;  // out / bias / FiLM / residual rows can be accessed as aligned float4 (conv_epilogue4)
 };
 
 // bias -> activation -> FiLM -> residual -> (tf32 rounding) -> store, one output element
@@ -81,6 +82,49 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int64_t o, in
   }
   if (p.flags & PCC_CONV_ROUND_OUT_TF32) v = round_tf32(v);
   p.out[o * p.out_stride + col] = v;
+}
+
+// The same element-wise chain for four consecutive columns col .. col + 3 (col % 4 == 0, p.vec4 set): one 16-byte
+// access per operand and row instead of four 4-byte ones — the rows of a tile are scattered over the output
+// (mask-sorted tile order), so a warp's scalar store touches 16 sectors for 128 useful bytes.
+__device__ __forceinline__ void conv_epilogue4(const ConvParams& p, int64_t o, int64_t frow, int64_t rrow, int col,
+                                               float (&v)[4]) {
+  if (p.bias) {
+    const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+    v[0] = __fadd_rn(v[0], b.x); v[1] = __fadd_rn(v[1], b.y); v[2] = __fadd_rn(v[2], b.z); v[3] = __fadd_rn(v[3], b.w);
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    if (p.act == PCC_ACT_RELU)
+      v[j] = fmaxf(v[j], 0.0f);
+    else if (p.act == PCC_ACT_LEAKY)
+      v[j] = v[j] > 0.0f ? v[j] : __fmul_rn(v[j], p.slope);
+  }
+  if (p.film_c) {
+    float4 beta = make_float4(0.f, 0.f, 0.f, 0.f), gamma = beta;
+    if (frow >= 0) {
+      if (p.film_c == 1) {
+        const float b = __ldg(p.film + frow * 2), g = __ldg(p.film + frow * 2 + 1);
+        beta = make_float4(b, b, b, b);
+        gamma = make_float4(g, g, g, g);
+      } else {
+        beta = __ldg(reinterpret_cast<const float4*>(p.film + frow * 2 * p.film_c + col));
+        gamma = __ldg(reinterpret_cast<const float4*>(p.film + frow * 2 * p.film_c + p.film_c + col));
+      }
+    }
+    v[0] = __fadd_rn(__fmul_rn(v[0], beta.x), gamma.x); v[1] = __fadd_rn(__fmul_rn(v[1], beta.y), gamma.y);
+    v[2] = __fadd_rn(__fmul_rn(v[2], beta.z), gamma.z); v[3] = __fadd_rn(__fmul_rn(v[3], beta.w), gamma.w);
+  }
+  if (p.residual) {
+    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (rrow >= 0) r = __ldg(reinterpret_cast<const float4*>(p.residual + rrow * p.cout + col));
+    v[0] = __fadd_rn(v[0], r.x); v[1] = __fadd_rn(v[1], r.y); v[2] = __fadd_rn(v[2], r.z); v[3] = __fadd_rn(v[3], r.w);
+  }
+  if (p.flags & PCC_CONV_ROUND_OUT_TF32) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = round_tf32(v[j]);
+  }
+  *reinterpret_cast<float4*>(p.out + o * p.out_stride + col) = make_float4(v[0], v[1], v[2], v[3]);
 }
 
 // TK: input channels per stage (32; 4 for layers with cin <= 4, which would otherwise multiply 28
@@ -640,6 +684,19 @@ conv_exact_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
       const int64_t t = tile_base + rbase + 4 * i;
       if (t >= p.n_out) continue;
       const int64_t o = p.order ? (int64_t)__ldg(p.order + t) : t;
+      if constexpr (CN % 4 == 0) {
+        if (p.vec4) {  // cout % 4 == 0: a quad is inside the row or entirely outside
+#pragma unroll
+          for (int q = 0; q < CN / 4; ++q) {
+            const int col = co_base + cbase + 32 * q;
+            if (col < p.cout) {
+              const float4 v = *reinterpret_cast<const float4*>(p.out + o * p.out_stride + col);
+              acc[i][4 * q] = v.x; acc[i][4 * q + 1] = v.y; acc[i][4 * q + 2] = v.z; acc[i][4 * q + 3] = v.w;
+            }
+          }
+          continue;
+        }
+      }
 #pragma unroll
       for (int c = 0; c < CN; ++c) {
         const int col = co_base + cbase + ((CN == 8) ? ((c >> 2) * 32 + (c & 3)) : c);
@@ -712,6 +769,21 @@ conv_exact_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
     int64_t frow = o, rrow = o;
     if (p.film_c && p.film_rows) frow = __ldg(p.film_rows + o);
     if (p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
+    if constexpr (CN % 4 == 0) {
+      if (p.vec4) {
+#pragma unroll
+        for (int q = 0; q < CN / 4; ++q) {
+          const int col = co_base + cbase + 32 * q;
+          if (col >= p.cout) continue;
+          float v[4] = {acc[i][4 * q], acc[i][4 * q + 1], acc[i][4 * q + 2], acc[i][4 * q + 3]};
+          if (p.last)
+            conv_epilogue4(p, o, frow, rrow, col, v);
+          else
+            *reinterpret_cast<float4*>(p.out + o * p.out_stride + col) = make_float4(v[0], v[1], v[2], v[3]);
+        }
+        continue;
+      }
+    }
 #pragma unroll
     for (int c = 0; c < CN; ++c) {
       const int col = co_base + cbase + ((CN == 8) ? ((c >> 2) * 32 + (c & 3)) : c);
@@ -1049,6 +1121,189 @@ conv_thin_kernel(const ConvParams p, int tiles) {
   }
 }
 
+// Thin input, wide output (cin <= 4, cout > 16: the first q_predict layer 2 -> 128, the xyz/rgb input layer
+// 4 -> 64).  One CTA = 128 output rows x 128 output channels with the 8 x 8 register tile of the main kernel, but
+// WITHOUT its 27 nearly empty pipeline stages: the tile's whole gathered operand, 27 cin values per row, is
+// staged once (transposed, [27 cin][128 rows]), the layer's weights once per CTA ([27 cin][128]), and the 27 cin
+// rank-1 updates run back to back from shared memory (4 LDS.128 per 32 FFMA2, no barrier in between).  A warp
+// (32 rows x 64 columns) skips the offsets none of its rows has.  Same FMA chain per output element.
+template <int CIN>
+__global__ void __launch_bounds__(CE_THREADS, 2)
+conv_thin_wide_kernel(const ConvParams p, int tiles) {
+  constexpr int K = 27, KC = K * CIN, KH = 14;  // KH: offsets gathered per thread (two threads per row)
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float* sw = reinterpret_cast<float*>(smem_raw);              // [KC][128] columns co_base .. + 127
+  float* xs = sw + KC * CE_TM;                                 // [KC][128 rows]
+  uint32_t* bmask = reinterpret_cast<uint32_t*>(xs + KC * CE_TM);  // [4]: offsets present in each 32-row block
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int co_base = blockIdx.y * 128;
+  for (int i = tid; i < KC * 128; i += CE_THREADS) {
+    const int r = i >> 7, c = i & 127;
+    sw[i] = (co_base + c < p.cout) ? __ldg(p.weight + (int64_t)r * p.cout + co_base + c) : 0.0f;
+  }
+  const int tx = lane & 7, ty = lane >> 3;
+  const int wr = wid >> 1, wc = wid & 1;  // warp: tile rows 32 wr .. + 31, columns 64 wc .. + 63
+  const int r0 = wr * 32 + ty * 8;        // this thread's 8 consecutive tile rows
+  const int c0 = wc * 64 + tx * 4;        // columns c0 .. c0 + 3 and c0 + 32 .. c0 + 35
+  for (int b = blockIdx.x; b < tiles; b += gridDim.x) {
+    const unsigned tile = p.tile_order ? (unsigned)__ldg(p.tile_order + b) : (unsigned)b;
+    const int64_t tile_base = (int64_t)tile * CE_TM;
+    const uint32_t mask = p.tapmask ? (p.tapmask[tile] & p.kbits) : p.kbits;
+    if (mask == 0 && !p.first && !p.last) continue;  // CTA-uniform
+    __syncthreads();  // the previous tile's reads of xs / bmask are done
+    if (tid < 4) bmask[tid] = 0u;
+    __syncthreads();
+    {
+      const int row = tid & (CE_TM - 1), half = tid >> 7;
+      const int64_t t = tile_base + row;
+      const bool valid = t < p.n_out;
+      int ixs[KH];
+#pragma unroll
+      for (int j = 0; j < KH; ++j) {
+        const int k = half * KH + j;
+        ixs[j] = (k < K && valid && ((mask >> k) & 1u)) ? __ldg(p.nbr + (int64_t)k * p.nbr_stride + t) : -1;
+      }
+      uint32_t wm = 0;
+#pragma unroll
+      for (int j = 0; j < KH; ++j)
+        if (__ballot_sync(0xffffffffu, ixs[j] >= 0)) wm |= 1u << ((half * KH + j) & 31);
+      if (lane == 0 && wm) atomicOr(&bmask[row >> 5], wm);
+#pragma unroll
+      for (int j = 0; j < KH; ++j) {
+        const int k = half * KH + j;
+        if (k >= K) continue;
+        const bool has = ixs[j] >= 0;
+        const float* src = p.in + (int64_t)(has ? ixs[j] : 0) * CIN;
+        float v[CIN];
+        if constexpr (CIN == 4) {
+          float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (has) q = __ldg(reinterpret_cast<const float4*>(src));
+          v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+        } else if constexpr (CIN == 2) {
+          float2 q = make_float2(0.f, 0.f);
+          if (has) q = __ldg(reinterpret_cast<const float2*>(src));
+          v[0] = q.x; v[1] = q.y;
+        } else {
+#pragma unroll
+          for (int ci = 0; ci < CIN; ++ci) {
+            v[ci] = 0.f;
+            if (has) v[ci] = __ldg(src + ci);
+          }
+        }
+#pragma unroll
+        for (int ci = 0; ci < CIN; ++ci) xs[(k * CIN + ci) * CE_TM + row] = v[ci];
+      }
+    }
+    __syncthreads();
+    if (co_base + wc * 64 >= p.cout) continue;  // a warp whose 64 columns lie beyond cout (cout <= 64) only gathers
+    const uint32_t wmask = bmask[wr];
+
+    float acc[8][8];
+    unsigned long long acc2[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int c = 0; c < 8; ++c) acc[i][c] = 0.0f;
+    if (!p.first) {  // continue the chains of the previous offset group
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int64_t t = tile_base + r0 + i;
+        if (t >= p.n_out) continue;
+        const int64_t o = p.order ? (int64_t)__ldg(p.order + t) : t;
+        if (p.vec4) {
+#pragma unroll
+          for (int q = 0; q < 2; ++q) {
+            const int col = co_base + c0 + 32 * q;
+            if (col < p.cout) {
+              const float4 v = *reinterpret_cast<const float4*>(p.out + o * p.out_stride + col);
+              acc[i][4 * q] = v.x; acc[i][4 * q + 1] = v.y; acc[i][4 * q + 2] = v.z; acc[i][4 * q + 3] = v.w;
+            }
+          }
+          continue;
+        }
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const int col = co_base + c0 + (c >> 2) * 32 + (c & 3);
+          if (col < p.cout) acc[i][c] = p.out[o * p.out_stride + col];
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) acc2[i][c] = pack2(acc[i][2 * c], acc[i][2 * c + 1]);
+#pragma unroll 1  // a rolled loop: 27 cin unrolled bodies of 32 FFMA2 would not fit the instruction cache
+    for (int k = 0; k < K; ++k) {
+      if (!((wmask >> k) & 1u)) continue;  // warp-uniform: every lane would add fma(0, w, acc) = acc
+#pragma unroll
+      for (int ci = 0; ci < CIN; ++ci) {
+        const float* xr = xs + (k * CIN + ci) * CE_TM + r0;
+        const float4 xa = *reinterpret_cast<const float4*>(xr);
+        const float4 xb = *reinterpret_cast<const float4*>(xr + 4);
+        const float* wrow = sw + (k * CIN + ci) * 128 + c0;
+        const float4 w0 = *reinterpret_cast<const float4*>(wrow);
+        const float4 w1 = *reinterpret_cast<const float4*>(wrow + 32);
+        const unsigned long long bp[4] = {pack2(w0.x, w0.y), pack2(w0.z, w0.w), pack2(w1.x, w1.y), pack2(w1.z, w1.w)};
+        const float xv[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const unsigned long long aa = pack2(xv[i], xv[i]);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) ffma2(acc2[i][c], aa, bp[c]);
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) unpack2(acc2[i][c], acc[i][2 * c], acc[i][2 * c + 1]);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int64_t t = tile_base + r0 + i;
+      if (t >= p.n_out) continue;
+      const int64_t o = p.order ? (int64_t)__ldg(p.order + t) : t;
+      int64_t frow = o, rrow = o;
+      if (p.film_c && p.film_rows) frow = __ldg(p.film_rows + o);
+      if (p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
+      if (p.vec4) {
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+          const int col = co_base + c0 + 32 * q;
+          if (col >= p.cout) continue;
+          float v[4] = {acc[i][4 * q], acc[i][4 * q + 1], acc[i][4 * q + 2], acc[i][4 * q + 3]};
+          if (p.last)
+            conv_epilogue4(p, o, frow, rrow, col, v);
+          else
+            *reinterpret_cast<float4*>(p.out + o * p.out_stride + col) = make_float4(v[0], v[1], v[2], v[3]);
+        }
+        continue;
+      }
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const int col = co_base + c0 + (c >> 2) * 32 + (c & 3);
+        if (col >= p.cout) continue;
+        if (p.last)
+          conv_epilogue(p, o, frow, rrow, col, acc[i][c]);
+        else
+          p.out[o * p.out_stride + col] = acc[i][c];
+      }
+    }
+  }
+}
+
+template <int CIN>
+static int launch_thin_wide(const ConvParams& p, cudaStream_t st) {
+  const size_t smem = (size_t)2 * 27 * CIN * CE_TM * 4 + 16;
+  const int tiles = (int)ceil_div(p.n_out, CE_TM);
+  const int gx = tiles < 2 * sm_count() ? tiles : 2 * sm_count();
+  static const cudaError_t attr =
+      cudaFuncSetAttribute(conv_thin_wide_kernel<CIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  PCC_CHECK_CUDA(attr);
+  conv_thin_wide_kernel<CIN><<<dim3((unsigned)gx, (unsigned)ceil_div(p.cout, 128)), CE_THREADS, smem, st>>>(p, tiles);
+  PCC_CHECK_LAUNCH("conv_thin_wide_kernel");
+  return PCC_OK;
+}
+
 // -> PCC_OK when launched, 1 when this call is not a thin-input shape (the caller falls through)
 template <int CIN>
 static int launch_thin_cin(const ConvParams& p, cudaStream_t st) {
@@ -1077,10 +1332,16 @@ static int launch_thin(const ConvParams& p, cudaStream_t st) {
     const char* e = getenv("PCC_EXACT_THIN");
     return e ? atoi(e) : 1;
   }();
-  // cout > 16 stays on the tiled kernel: with x[27][cin] in registers there is no room to keep enough weight
-  // loads in flight, and the column passes run at the shared-memory latency (measured 2 -> 128 on 249,574 rows:
-  // 0.57 ms here vs 0.42 ms tiled; 4 -> 64 on 799,458 rows: 0.61 vs 0.43 ms; PCC_EXACT_THIN=2 forces them here)
-  if (!on || p.K != 27 || p.cin < 1 || p.cin > 4 || p.n_out >= (1ll << 31) - CE_TM || (p.cout > 16 && on < 2)) return 1;
+  if (!on || p.K != 27 || p.cin < 1 || p.cin > 4 || p.n_out >= (1ll << 31) - CE_TM) return 1;
+  if (p.cout > 16 && on < 2) {  // PCC_EXACT_THIN=2: the row-per-thread kernel for every width (A/B timing)
+    const uintptr_t ai = reinterpret_cast<uintptr_t>(p.in);
+    switch (p.cin) {
+      case 1: return launch_thin_wide<1>(p, st);
+      case 2: return (ai & 7) ? 1 : launch_thin_wide<2>(p, st);
+      case 3: return launch_thin_wide<3>(p, st);
+      default: return (ai & 15) ? 1 : launch_thin_wide<4>(p, st);
+    }
+  }
   const uintptr_t a = reinterpret_cast<uintptr_t>(p.in);
   switch (p.cin) {
     case 1: return launch_thin_cin<1>(p, st);
@@ -1182,6 +1443,11 @@ int conv_exact(const pcc_conv_args* a, cudaStream_t st) {
   p.cin = a->cin; p.cout = a->cout; p.K = a->K; p.act = a->act; p.film_c = a->film_c; p.slope = a->slope; p.flags = a->flags;
   const uint32_t kfull = p.K >= 32 ? 0xffffffffu : ((1u << p.K) - 1u);
   p.tile_order = a->tile_order;
+  {
+    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    p.vec4 = p.cout % 4 == 0 && p.out_stride % 4 == 0 && al16(p.out) && al16(p.bias) && al16(p.residual) &&
+             (!p.film_c || (al16(p.film) && (p.film_c == 1 || p.film_c % 4 == 0)));
+  }
   const int ng = a->n_groups > 1 ? a->n_groups : 1;
   if (ng == 1) {
     p.kbits = kfull; p.first = 1; p.last = 1;

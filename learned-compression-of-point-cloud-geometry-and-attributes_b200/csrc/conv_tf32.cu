@@ -379,6 +379,9 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
     if (live && p.film_c && p.film_rows) frow = __ldg(p.film_rows + o);
     if (live && p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
     const bool vec4 = (p.out_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
+    const bool fvec = p.cout % 4 == 0 && (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0 &&
+                      (reinterpret_cast<uintptr_t>(p.residual) & 15) == 0 &&
+                      (!p.film_c || ((reinterpret_cast<uintptr_t>(p.film) & 15) == 0 && (p.film_c == 1 || p.film_c % 4 == 0)));
 #pragma unroll 1
     for (int c0 = (warp >> 2) * EPI_COLS; c0 < ((warp >> 2) + 1) * EPI_COLS && c0 < BN; c0 += 32) {
       if (co_base + c0 >= p.cout) break;  // warp-uniform
@@ -389,7 +392,52 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = 0u;
       }
-      if (live) {
+      if (live && vec4 && co_base + c0 + 32 <= p.cout && fvec) {
+        // 16-byte accesses for every per-row operand: this thread owns 32 consecutive columns of one output row
+        float* dst = p.out + o * p.out_stride + co_base + c0;
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          const int col = co_base + c0 + i;
+          float x[4] = {__uint_as_float(v[i]), __uint_as_float(v[i + 1]), __uint_as_float(v[i + 2]),
+                        __uint_as_float(v[i + 3])};
+          if (p.bias) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+            x[0] = __fadd_rn(x[0], b.x); x[1] = __fadd_rn(x[1], b.y); x[2] = __fadd_rn(x[2], b.z); x[3] = __fadd_rn(x[3], b.w);
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (p.act == PCC_ACT_RELU)
+              x[j] = fmaxf(x[j], 0.0f);
+            else if (p.act == PCC_ACT_LEAKY)
+              x[j] = x[j] > 0.0f ? x[j] : __fmul_rn(x[j], p.slope);
+          }
+          if (p.film_c) {
+            float4 beta = make_float4(0.f, 0.f, 0.f, 0.f), gamma = beta;
+            if (frow >= 0) {
+              if (p.film_c == 1) {
+                const float b = __ldg(p.film + frow * 2), g = __ldg(p.film + frow * 2 + 1);
+                beta = make_float4(b, b, b, b);
+                gamma = make_float4(g, g, g, g);
+              } else {
+                beta = __ldg(reinterpret_cast<const float4*>(p.film + frow * 2 * p.film_c + col));
+                gamma = __ldg(reinterpret_cast<const float4*>(p.film + frow * 2 * p.film_c + p.film_c + col));
+              }
+            }
+            x[0] = __fadd_rn(__fmul_rn(x[0], beta.x), gamma.x); x[1] = __fadd_rn(__fmul_rn(x[1], beta.y), gamma.y);
+            x[2] = __fadd_rn(__fmul_rn(x[2], beta.z), gamma.z); x[3] = __fadd_rn(__fmul_rn(x[3], beta.w), gamma.w);
+          }
+          if (p.residual) {
+            float4 r4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (rrow >= 0) r4 = __ldg(reinterpret_cast<const float4*>(p.residual + rrow * p.cout + col));
+            x[0] = __fadd_rn(x[0], r4.x); x[1] = __fadd_rn(x[1], r4.y); x[2] = __fadd_rn(x[2], r4.z); x[3] = __fadd_rn(x[3], r4.w);
+          }
+          if (p.flags & PCC_CONV_ROUND_OUT_TF32) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) x[j] = round_tf32(x[j]);
+          }
+          *reinterpret_cast<float4*>(dst + i) = make_float4(x[0], x[1], x[2], x[3]);
+        }
+      } else if (live) {
         float r[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
@@ -655,6 +703,9 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
     if (live && p.film_c && p.film_rows) frow = __ldg(p.film_rows + o);
     if (live && p.residual && p.res_rows) rrow = __ldg(p.res_rows + o);
     const bool vec4 = (p.out_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
+    const bool fvec = p.cout % 4 == 0 && (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0 &&
+                      (reinterpret_cast<uintptr_t>(p.residual) & 15) == 0 &&
+                      (!p.film_c || ((reinterpret_cast<uintptr_t>(p.film) & 15) == 0 && (p.film_c == 1 || p.film_c % 4 == 0)));
 #pragma unroll 1
     for (int c0 = 0; c0 < BN; c0 += 32) {
       if (co_base + c0 >= p.cout) break;  // warp-uniform
@@ -665,7 +716,52 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = 0u;
       }
-      if (live) {
+      if (live && vec4 && co_base + c0 + 32 <= p.cout && fvec) {
+        // 16-byte accesses for every per-row operand: this thread owns 32 consecutive columns of one output row
+        float* dst = p.out + o * p.out_stride + co_base + c0;
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          const int col = co_base + c0 + i;
+          float x[4] = {__uint_as_float(v[i]), __uint_as_float(v[i + 1]), __uint_as_float(v[i + 2]),
+                        __uint_as_float(v[i + 3])};
+          if (p.bias) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+            x[0] = __fadd_rn(x[0], b.x); x[1] = __fadd_rn(x[1], b.y); x[2] = __fadd_rn(x[2], b.z); x[3] = __fadd_rn(x[3], b.w);
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (p.act == PCC_ACT_RELU)
+              x[j] = fmaxf(x[j], 0.0f);
+            else if (p.act == PCC_ACT_LEAKY)
+              x[j] = x[j] > 0.0f ? x[j] : __fmul_rn(x[j], p.slope);
+          }
+          if (p.film_c) {
+            float4 beta = make_float4(0.f, 0.f, 0.f, 0.f), gamma = beta;
+            if (frow >= 0) {
+              if (p.film_c == 1) {
+                const float b = __ldg(p.film + frow * 2), g = __ldg(p.film + frow * 2 + 1);
+                beta = make_float4(b, b, b, b);
+                gamma = make_float4(g, g, g, g);
+              } else {
+                beta = __ldg(reinterpret_cast<const float4*>(p.film + frow * 2 * p.film_c + col));
+                gamma = __ldg(reinterpret_cast<const float4*>(p.film + frow * 2 * p.film_c + p.film_c + col));
+              }
+            }
+            x[0] = __fadd_rn(__fmul_rn(x[0], beta.x), gamma.x); x[1] = __fadd_rn(__fmul_rn(x[1], beta.y), gamma.y);
+            x[2] = __fadd_rn(__fmul_rn(x[2], beta.z), gamma.z); x[3] = __fadd_rn(__fmul_rn(x[3], beta.w), gamma.w);
+          }
+          if (p.residual) {
+            float4 r4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (rrow >= 0) r4 = __ldg(reinterpret_cast<const float4*>(p.residual + rrow * p.cout + col));
+            x[0] = __fadd_rn(x[0], r4.x); x[1] = __fadd_rn(x[1], r4.y); x[2] = __fadd_rn(x[2], r4.z); x[3] = __fadd_rn(x[3], r4.w);
+          }
+          if (p.flags & PCC_CONV_ROUND_OUT_TF32) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) x[j] = round_tf32(x[j]);
+          }
+          *reinterpret_cast<float4*>(dst + i) = make_float4(x[0], x[1], x[2], x[3]);
+        }
+      } else if (live) {
         float r[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
