@@ -219,6 +219,9 @@ __global__ void expand_emit_kernel(const uint64_t* __restrict__ keys, int64_t n,
 // MASK_ONLY: one thread per output row (natural order) -> its neighbour mask over all K offsets.
 // Otherwise: one thread per TILE ROW j of offset group [k_lo, k_hi): output row o = order[j], writes
 // nbr[k][j] for the group's offsets and the tile's tap mask (bits k_lo .. k_hi - 1 only).
+// ints per row of the mask pass's probe results: a multiple of 4 (16-byte accesses); 32 = one 128-byte line for K = 27
+__host__ __device__ constexpr int km_found_pitch(int K) { return K > 16 ? 32 : ((K + 3) & ~3); }
+
 template <int KS, bool MASK_ONLY>
 __global__ void __launch_bounds__(PCC_TILE_M)
 kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict__ tvals,
@@ -246,18 +249,35 @@ kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict_
   // write pass after a mask pass: the row's mask says which neighbours exist, so the (longer) probe sequences
   // of the missing ones are not walked a second time
   const uint32_t known = (!MASK_ONLY && row_masks && live) ? __ldg(row_masks + o_row) : 0xffffffffu;
-#pragma unroll 3
-  for (int k = 0; k < K; ++k) {
-    if (!MASK_ONLY && (k < k_lo || k >= k_hi)) continue;
+  auto probe = [&](int k) {
     const int dx = k % KS + LO, dy = (k / KS) % KS + LO, dz = k / (KS * KS) + LO;
     const int qx = x + dx * step, qy = y + dy * step, qz = z + dz * step;
     int r = -1;
     if (live && ((known >> k) & 1u) && coord_in_range(qx) && coord_in_range(qy) && coord_in_range(qz) &&
         (((qx | qy | qz) & amask) == 0))
       r = hash_find(tkeys, tvals, cap_mask, pack_key(b, qx, qy, qz));
-    if (!MASK_ONLY && live) nbr[(int64_t)k * nbr_stride + j] = r;
-    if (MASK_ONLY && found && live) found[(int64_t)k * n_out + j] = r;  // [K][n_out], output-row order
     if (r >= 0) mine |= 1u << k;
+    return r;
+  };
+  if (MASK_ONLY && found) {
+    // probe results kept ROW-major, found[row][KM_FOUND_PITCH], written 16 bytes at a time: the write pass reads a
+    // row by its tile position (a random row), and a row's 27 entries are then four whole sectors instead of
+    // 27 sectors with 4 useful bytes each
+    constexpr int FP = km_found_pitch(K);
+#pragma unroll 1
+    for (int k4 = 0; k4 < FP; k4 += 4) {
+      int r[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) r[e] = (k4 + e < K) ? probe(k4 + e) : -1;
+      if (live) *reinterpret_cast<int4*>(found + j * FP + k4) = make_int4(r[0], r[1], r[2], r[3]);
+    }
+  } else {
+#pragma unroll 3
+    for (int k = 0; k < K; ++k) {
+      if (!MASK_ONLY && (k < k_lo || k >= k_hi)) continue;
+      const int r = probe(k);
+      if (!MASK_ONLY && live) nbr[(int64_t)k * nbr_stride + j] = r;
+    }
   }
   if (MASK_ONLY) {
     if (live) row_masks[j] = mine;
@@ -270,7 +290,7 @@ kernel_map_kernel(const uint64_t* __restrict__ tkeys, const int32_t* __restrict_
   if (threadIdx.x == 0 && tapmask) tapmask[blockIdx.x] = smask;
 }
 
-// Write pass after a mask pass that kept its probe results (found: [K][n_out] in output-row order): tile row j of
+// Write pass after a mask pass that kept its probe results (found: [n_out][km_found_pitch(K)], output-row order): tile row j of
 // the group takes the entries of output row order[j] — a permuted copy, no second walk through the hash table —
 // and the warp votes the tile's tap mask as kernel_map_kernel does.
 template <int KS>
@@ -286,11 +306,19 @@ kernel_map_permute_kernel(const int32_t* __restrict__ found, int64_t n_out, cons
   const bool live = j < n_out;
   const int64_t o = live ? (int64_t)__ldg(order + j) : 0;
   uint32_t mine = 0;
+  constexpr int FP = km_found_pitch(K);
+  int32_t vals[FP];
+#pragma unroll
+  for (int q = 0; q < FP / 4; ++q) {
+    int4 v = make_int4(-1, -1, -1, -1);
+    if (live && 4 * q < k_hi && 4 * q + 3 >= k_lo) v = __ldg(reinterpret_cast<const int4*>(found + o * FP) + q);
+    vals[4 * q] = v.x; vals[4 * q + 1] = v.y; vals[4 * q + 2] = v.z; vals[4 * q + 3] = v.w;
+  }
 #pragma unroll
   for (int k = 0; k < K; ++k) {
     if (k < k_lo || k >= k_hi) continue;
     if (live) {
-      const int32_t r = __ldg(found + (int64_t)k * n_out + o);
+      const int32_t r = vals[k];
       nbr[(int64_t)k * nbr_stride + j] = r;
       if (r >= 0) mine |= 1u << k;
     }
@@ -573,9 +601,9 @@ int pcc_coords_expand(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, 
 
 size_t pcc_kernel_map_ws_bytes(int64_t n_out) {
   if (n_out <= 0) return 256;
-  // sort keys in | sort keys out | iota | row masks | cub | two counters | the mask pass's probe results [27][n_out]
+  // sort keys in | sort keys out | iota | row masks | cub | two counters | the mask pass's probe results [n_out][32]
   return align_up((size_t)n_out * 8, 256) * 2 + align_up((size_t)n_out * 4, 256) * 2 +
-         align_up(cub_sort_pairs_bytes(n_out), 256) + 256 + align_up((size_t)n_out * 27 * 4, 256);
+         align_up(cub_sort_pairs_bytes(n_out), 256) + 256 + align_up((size_t)n_out * 32 * 4, 256);
 }
 
 }  // extern "C"
