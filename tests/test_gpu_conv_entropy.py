@@ -58,11 +58,14 @@ def test_conv_variants_bitwise(pcc, oracle, ks, stride, transpose):
 
 
 @pytest.mark.parametrize("cin,cout,film_c", [(24, 48, 0), (24, 48, 1), (24, 48, 48),
-                                             (64, 4, 0), (64, 4, 1), (64, 4, 4), (128, 3, 3), (40, 2, 1), (16, 1, 1)])
+                                             (64, 4, 0), (64, 4, 1), (64, 4, 4), (128, 3, 3), (40, 2, 1), (16, 1, 1),
+                                             # conv_exact_tma_kernel <64,4> / <128,8>: 16-byte epilogue (conv_epilogue4)
+                                             (64, 64, 64), (32, 64, 1), (64, 128, 128), (128, 256, 0), (64, 36, 36)])
 @pytest.mark.parametrize("act", [0, 1, 2])
 def test_conv_epilogue_bitwise(pcc, oracle, cin, cout, film_c, act):
     """bias -> activation -> FiLM (x*beta+gamma, model/blocks.py:40) -> residual (model/blocks.py:50);
-    cout <= 4 with cin % 4 == 0 runs the narrow-output kernel (conv_head_kernel)."""
+    cout <= 4 with cin % 4 == 0 runs the narrow-output kernel (conv_head_kernel); cin % 32 == 0 with a 64- or
+    128-wide tile the TMA kernel, whose epilogue moves four columns per access."""
     rng = np.random.default_rng(film_c + act + cin)
     m, keys, cs = _setup(pcc, oracle, 2500, 20, 1, 5)
     n = m.n
