@@ -13,6 +13,8 @@ translations: each block runs as a fused plan over ``ops`` —
     coordinates, z_hat taken from the quantiser instead of decoding the string just encoded.
 Each method cites the reference lines it follows.
 """
+import os
+
 import torch
 import torch.nn as nn
 
@@ -25,9 +27,13 @@ from .slab import SlabMap
 
 RELU, LEAKY, NONE = ops.ACT_RELU, ops.ACT_LEAKY, ops.ACT_NONE
 
-# Optional stage timer (tools/stage_profile.py): when set to a dict, every `with stage(name)` block
-# is bracketed by device synchronisations and its wall time accumulated.  Off (None) on the hot path.
+# Optional stage instrumentation, off on the hot path:
+#  * STAGE_MS (tools/stage_profile.py): when set to a dict, every `with stage(name)` block is bracketed by device
+#    synchronisations and its wall time accumulated;
+#  * PCC_NVTX=1 in the environment: every stage is an NVTX range (torch.cuda.nvtx), so an `ncu --nvtx` / Nsight
+#    Systems capture shows g_a, h_a, the coders, h_s and the three up-sampling stages by name.
 STAGE_MS = None
+NVTX = os.environ.get("PCC_NVTX", "0") == "1"
 
 
 class stage:
@@ -35,6 +41,8 @@ class stage:
         self.name = name
 
     def __enter__(self):
+        if NVTX:
+            torch.cuda.nvtx.range_push(self.name)
         if STAGE_MS is not None:
             import time
             torch.cuda.synchronize()
@@ -45,6 +53,8 @@ class stage:
             import time
             torch.cuda.synchronize()
             STAGE_MS[self.name] = STAGE_MS.get(self.name, 0.0) + (time.perf_counter() - self.t0) * 1e3
+        if NVTX:
+            torch.cuda.nvtx.range_pop()
         return False
 
 

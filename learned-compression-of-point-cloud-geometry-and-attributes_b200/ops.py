@@ -268,7 +268,7 @@ class CoordMap:
 # Rows per segment of the tile-row sort (0 = keep lexicographic tiles).  None = by mode: the exact
 # (FP32-pipe-bound) path sorts whole maps; the tensor-core path keeps a tile's gathers inside an
 # L2-sized segment of the map.
-_tile_seg_rows = None
+_tile_seg_rows = int(os.environ["PCC_TILE_SEG_ROWS"]) if "PCC_TILE_SEG_ROWS" in os.environ else None  # A/B override
 
 
 def set_tile_segment_rows(n):

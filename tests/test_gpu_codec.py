@@ -57,6 +57,22 @@ def test_compress_decompress_bit_exact(pcc, oracle, config_name, radius, seed, q
     assert torch.equal(model.last["y_hat"].F, y_hat_enc)
 
 
+def test_nvtx_stage_ranges_do_not_change_results(pcc, oracle, monkeypatch):
+    """PCC_NVTX=1 (named ranges around the stages) only pushes / pops NVTX ranges."""
+    model, oc, got, ref, x = _run(pcc, oracle, pcc.OURS_CONFIG, 14.0, 3)
+    pushed = []
+    real_push = torch.cuda.nvtx.range_push
+    monkeypatch.setattr(pcc.codec, "NVTX", True)
+    monkeypatch.setattr(torch.cuda.nvtx, "range_push", lambda name: (pushed.append(name), real_push(name))[1])
+    qc, qf = pcc.synthetic.uniform_q_map(x, 0.5, 0.5)
+    strings, shape, k, coords = model.compress(x.to(DEV), (qc.to(DEV), qf.to(DEV)))
+    out = model.decompress(coordinates=coords, strings=strings, shape=shape, k=k)
+    assert strings == got[0] == ref[0]
+    assert np.array_equal(out.cpu().numpy(), oc.decompress(ref[3], ref[0], ref[1], ref[2]))
+    for name in ("enc.g_a", "enc.h_a", "enc.y_coder", "dec.z_coder", "g_s.stage1.up", "dec.finalize"):
+        assert name in pushed, (name, pushed)
+
+
 def test_decompress_accepts_float_unsorted_coordinates(pcc, oracle):
     """model/model.py:184-188 hands float coordinates to ME; order must not matter."""
     model, oc, got, ref, x = _run(pcc, oracle, pcc.OURS_CONFIG, 18.0, 5)
