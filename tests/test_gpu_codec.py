@@ -69,7 +69,7 @@ def test_nvtx_stage_ranges_do_not_change_results(pcc, oracle, monkeypatch):
     out = model.decompress(coordinates=coords, strings=strings, shape=shape, k=k)
     assert strings == got[0] == ref[0]
     assert np.array_equal(out.cpu().numpy(), oc.decompress(ref[3], ref[0], ref[1], ref[2]))
-    for name in ("enc.g_a", "enc.h_a", "enc.y_coder", "dec.z_coder", "g_s.stage1.up", "dec.finalize"):
+    for name in ("enc.g_a", "enc.h_a", "enc.z_coder", "enc.h_s", "dec.z_coder", "dec.h_q+h_s", "g_s.stage1.up", "dec.finalize"):
         assert name in pushed, (name, pushed)
 
 
