@@ -1384,17 +1384,17 @@ static int launch_exact(const ConvParams& p, cudaStream_t st) {
   if constexpr (TN >= 64) {
     const int tma = exact_tma();
     if (vec && f2 != 0 && p.cin % CE_TK == 0 && (tma >= 2 || (tma == 1 && TN == 128))) {
-      // 64-wide tiles: 128 threads with 8 x 8 register tiles (3 CTAs per SM) for the large same-map layers, where
-      // they are 3.8 % faster (3 x 64->64 on the 3.98 M candidates: 36.7 -> 35.3 ms); 256 threads with 8 x 4 tiles
-      // elsewhere (short tiles — the generative transposed convolution has 1-8 active offsets per tile — and
-      // surface levels run 5-30 % faster on them).  PCC_EXACT_TMA64 = 8 / 4 forces one shape, 0 = this rule.
+      // 64-wide tiles: 128 threads with 8 x 8 register tiles (3 CTAs per SM) for maps of >= 262,144 rows (with the
+      // 16-byte epilogue: 3 x 64->64 on the 3.98 M candidates 36.7 -> 33.6 ms, 64->64 on 799,458 rows 1.80 -> 1.68,
+      // the generative 128->64 2.45 -> 2.33); 256 threads with 8 x 4 tiles on the smaller levels, which cannot
+      // fill 3 x 148 four-warp CTAs (17,957 rows: 3.63 vs 3.73 ms).  PCC_EXACT_TMA64 = 8 / 4 forces one shape.
       static const int cn64 = [] {
         const char* e = getenv("PCC_EXACT_TMA64");
         return e ? atoi(e) : 0;
       }();
       int rc;
       if constexpr (TN == 64)
-        rc = (cn64 == 8 || (cn64 == 0 && p.n_in == p.n_out && p.n_out >= (2ll << 20)))
+        rc = (cn64 == 8 || (cn64 == 0 && p.n_out >= (1ll << 18)))
                  ? launch_exact_tma<64, 8>(p, p.n_in, st)
                  : launch_exact_tma<64, 4>(p, p.n_in, st);
       else
