@@ -113,19 +113,19 @@ __global__ void compact_heads_kernel(const uint64_t* __restrict__ sorted, int64_
 // Candidate q = p + d * ts_out (ts_out = ts_in / 2).  Along an axis with d != 0, q lies between
 // p and p + 2 d ts_out, so the parents that also generate q are p + (e .* d) * ts_in for
 // e in {0,1}^3 (e_a = 0 where d_a = 0).  p owns q iff none of those that is lexicographically
-// smaller than p exists.  The alternatives are among p's 26 coarse neighbours, so one
-// 27-neighbour probe per parent decides ownership of all 27 candidates.
+// smaller than p exists.  The alternatives are among p's 13 lexicographically smaller coarse neighbours,
+// so 13 probes per parent decide ownership of all 27 candidates.
 __device__ __forceinline__ uint32_t coarse_neighbour_mask(const uint64_t* tkeys, const int32_t* tvals,
                                                           uint64_t cap_mask, int b, int x, int y, int z,
                                                           int ts) {
-  uint32_t m = 0;
-#pragma unroll 1
+  uint32_t m = 1u << 13;
+  // ownership only asks about the lexicographically SMALLER coarse neighbours (owned_candidates reads no other
+  // bit): 13 of the 26, probed as independent, fully unrolled sequences so that they are in flight together
+#pragma unroll
   for (int k = 0; k < 27; ++k) {
     const int dx = k % 3 - 1, dy = (k / 3) % 3 - 1, dz = k / 9 - 1;
-    if (k == 13) {
-      m |= 1u << 13;
-      continue;
-    }
+    const int first = dx != 0 ? dx : (dy != 0 ? dy : dz);
+    if (first >= 0) continue;  // compile-time
     const int qx = x + dx * ts, qy = y + dy * ts, qz = z + dz * ts;
     if (coord_in_range(qx) && coord_in_range(qy) && coord_in_range(qz) &&
         hash_find(tkeys, tvals, cap_mask, pack_key(b, qx, qy, qz)) >= 0)
