@@ -45,12 +45,11 @@ def parse_args():
     ap.add_argument("--frames-per-step", type=int, default=12,
                     help="frames coded per step per GPU (frame pipeline; 1 = one frame at a time)")
     ap.add_argument("--depth", type=int, default=0,
-                    help="frames in flight per GPU; 0 = 6 when this rank's share of the host cores covers six launch "
-                         "threads and a coder thread, else 4 (measured, same box, 799,458-point frame: depth 4 / 6 / 8 = "
+                    help="frames in flight per GPU; 0 = 6 (measured on the 16-core box, 799,458-point frame: depth 4 / 6 / 8 = "
                          "4.90 / 5.13 / - M points/s exact, 15.7 / 17.9 / 15.3 M tf32)")
     ap.add_argument("--scheduler", default="auto", choices=["auto", "threads", "cooperative"],
                     help="frame pipeline: one launch thread per in-flight frame, or one thread resuming all frames; "
-                         "auto = threads when this rank's share of the host cores covers its launch and coder threads")
+                         "auto = threads when this rank's share of the host cores is at least 4")
     ap.add_argument("--no-tf32-pass", action="store_true",
                     help="skip the secondary tensor-core (tf32) measurement added to the exact-mode line")
     ap.add_argument("--no-scene-pass", action="store_true",
@@ -467,12 +466,14 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.set_device(dev)
     ops.set_default_mode(ops.MODE_TF32 if args.mode == "tf32" else ops.MODE_EXACT)
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    per_rank = cores // max(1, world)
     if args.depth <= 0:
-        args.depth = 6 if cores // max(1, world) >= 7 else 4
+        args.depth = 6
     if args.scheduler == "auto":
-        # every launch thread spins in its CUDA waits: with fewer host cores per rank than in-flight frames plus
-        # a coder thread the threads would fight each other, and the single-thread scheduler is the better one
-        args.scheduler = "threads" if cores // max(1, world) >= args.depth + 1 else "cooperative"
+        # one launch thread per in-flight frame needs a few cores of its own (the threads wait on CUDA events and
+        # on the coder); measured on ONE GPU pinned to 4 cores (taskset -c 0-3, 799,458-point frame, exact):
+        # cooperative depth 4 / 6 / 8 = 4.72 / 4.84 / 4.83 M points/s, threads depth 3 / 4 / 6 = 4.80 / 4.97 / 5.05 M
+        args.scheduler = "threads" if per_rank >= 4 else "cooperative"
     model, cfg = make_model(args.config, dev)
     peaks = {}
     try:
