@@ -71,8 +71,10 @@ class ClockSampler:
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index):
-        self.gpu = gpu_index
+    def __init__(self, gpu_index, n_gpus=1):
+        # every GPU of the job is sampled (rank r uses GPU r of the node): the step time is the max over ranks, so
+        # one throttled GPU is enough to slow the job
+        self.gpus = list(range(n_gpus)) if n_gpus > 1 else [gpu_index]
         self.proc = None
         self.path = None
 
@@ -82,7 +84,7 @@ class ClockSampler:
             os.close(fd)
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
-                 "-i", str(self.gpu)], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+                 "-i", ",".join(str(g) for g in self.gpus)], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
 
@@ -94,24 +96,30 @@ class ClockSampler:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-        sm, smax, reasons = [], [], set()
+        sm, smax, power, reasons = {}, [], {}, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in open(self.path):
             f = [v.strip() for v in line.split(",")]
             if len(f) < 9:
                 continue
             try:
-                sm.append(float(f[1]))
+                g = int(f[0])
+                sm.setdefault(g, []).append(float(f[1]))
                 smax.append(float(f[2]))
+                power.setdefault(g, []).append(float(f[3]))
             except ValueError:
                 continue
             for name, v in zip(names, f[5:9]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
         os.unlink(self.path)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(smax) if smax else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        med = {g: sorted(v)[len(v) // 2] for g, v in sm.items()}
+        out = {"sm_mhz": min(med.values()) if med else None, "sm_max_mhz": max(smax) if smax else None,
+               "samples": sum(len(v) for v in sm.values()), "reasons": sorted(reasons)}
+        if len(med) > 1:  # sm_mhz = the slowest GPU's median under load
+            out["per_gpu_sm_mhz"] = [med[g] for g in sorted(med)]
+            out["per_gpu_power_w"] = [round(sorted(power[g])[len(power[g]) // 2], 1) for g in sorted(power)]
+        return out
 
 
 # ------------------------------------------------------------------------------ workload
@@ -396,7 +404,7 @@ def measure_scene(args, rank, world, local_rank, model, steps, warmup, verify):
         gc.collect()
         gc.disable()
         barrier()
-        sampler = ClockSampler(local_rank)
+        sampler = ClockSampler(local_rank, world)
         if rank == 0 and name == "dev":
             sampler.start()
         l0 = ops.launches()
@@ -530,7 +538,7 @@ def run_ours(args, rank, world, local_rank):
     gc.collect()
     gc.disable()  # no collector pauses inside the timed regions (re-enabled after the e2e loop)
     barrier()
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(local_rank, world)
     if rank == 0:
         sampler.start()
     cc.reset_coder_stats()
