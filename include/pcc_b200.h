@@ -107,8 +107,9 @@ int pcc_coords_expand(const uint64_t* tkeys, const int32_t* tvals, int64_t cap, 
  * nbr[k] is indexed by the tile rows of k's group.  pcc_conv_fwd then runs one pass per group,
  * continuing every output element's FMA chain from the previous pass, so results do not change.
  * n_groups == 0 chooses: the rows are sorted by the whole mask, the share of useful MACs of such
- * tiles is measured on the device, and one group is kept when it is >= 0.72, else 3 groups are
- * built; order / tapmask must be sized for 3 groups and the stream is synchronised to read the
+ * tiles is measured on the device, and one group is kept when it is >= 0.90 or the map has fewer
+ * than 2 x SM-count tiles; two groups are built down to 0.70 and three below; order / tapmask /
+ * tile_order must be sized for 3 groups and the stream is synchronised to read the
  * measurement.  *n_groups_used [host, may be NULL unless n_groups == 0] receives the group count.
  * tile_order [dev, n_groups x ceil(n_out / PCC_TILE_M), may be NULL; needs tapmask] RECEIVES, per
  * group, the tiles sorted by descending number of active offsets: the convolution's CTA b works on
